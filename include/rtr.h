@@ -1,0 +1,259 @@
+/*
+ * rtr.h — C ABI of the B200 render hot path (librtr_b200.so).
+ *
+ * This is the drop-in boundary for the reference crate's
+ *     pub fn render(target: &mut RenderTarget, scene: &Scene)      (lib/core/render.rs:61)
+ * and for everything that call consumes.  The reference has no FFI of its own; the
+ * Rust-side `lower()` pass walks the crate's `Scene` into the plain
+ * structs below and calls these entry points.  No torch / C++ types appear here.
+ *
+ * Each struct cites the reference type it replaces (paths relative to the reference
+ * checkout).  All floating point is IEEE f32 (lib/utils/types.rs:4).
+ *
+ * Ownership: every pointer passed IN is borrowed for the duration of the call only
+ * (the library copies what it needs); every handle passed OUT is owned by the
+ * library until the matching *_destroy.  Output buffers are caller-allocated.
+ * Errors: never unwinds; returns rtr_status, message via rtr_last_error().
+ * Threading: a context is not re-entrant; distinct contexts are independent.
+ */
+#ifndef RTR_H_
+#define RTR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTR_ABI_VERSION 1u
+#define RTR_NO_HIT 0xFFFFFFFFu
+
+typedef enum rtr_status {
+    RTR_OK = 0,
+    RTR_INVALID_ARG = 1,  /* the reference would panic (unwrap/expect/index) */
+    RTR_CUDA_ERROR = 2,
+    RTR_OOM = 3,
+    RTR_UNSUPPORTED = 4,  /* e.g. Volume whose boundary is another Volume */
+    RTR_IO_ERROR = 5
+} rtr_status;
+
+/* cgmath::Vector3<f32> (lib/utils/types.rs:8) and Color (lib/utils/color.rs:6-11) */
+typedef struct rtr_vec3 { float x, y, z; } rtr_vec3;
+
+/* Camera (lib/core/camera.rs:27-34) */
+typedef struct rtr_camera {
+    rtr_vec3 lookfrom, lookat, vertical;
+    float vertical_fov;  /* degrees */
+    float aspect_ratio;  /* independent of W/H, as in the reference */
+} rtr_camera;
+
+/* RenderMode (lib/core/scene.rs:15-20), serde names "Full","Clay","Random","Normal" */
+enum { RTR_MODE_FULL = 0, RTR_MODE_CLAY = 1, RTR_MODE_RANDOM = 2, RTR_MODE_NORMAL = 3 };
+
+/* RenderSettings (lib/core/scene.rs:23-30); defaults 5/6/10.0/true/true/Full (:52-59) */
+typedef struct rtr_settings {
+    uint32_t samples_per_pixel;
+    uint32_t max_ray_depth;          /* u8 in the reference: 0..255 */
+    float clamp_indirect;
+    uint32_t enable_multithreading;  /* accepted, ignored on device */
+    uint32_t enable_bvh_tree;        /* 0 = Hittable for Scene linear scan (scene.rs:141-156) */
+    uint32_t mode;                   /* RTR_MODE_* */
+} rtr_settings;
+
+/* Box<dyn Object> (lib/core/traits.rs:17-20): tagged reference into the typed arrays */
+enum { RTR_OBJ_SPHERE = 0, RTR_OBJ_MESH = 1, RTR_OBJ_VOLUME = 2 };
+typedef struct rtr_object_ref { uint32_t kind, index; } rtr_object_ref;
+
+/* Sphere (lib/objects.rs:15-20) */
+typedef struct rtr_sphere { rtr_vec3 center; float radius; uint32_t material; } rtr_sphere;
+
+/* Mesh after Mesh::from_file/from_buffers + build_bvh() (lib/core/mesh.rs:31-38,63-121).
+ * positions/normals: 3 floats per vertex; indices: 3 per triangle (u32). */
+typedef struct rtr_mesh {
+    const float* positions;
+    const float* normals;
+    const uint32_t* indices;
+    uint32_t n_vertices;
+    uint32_t n_indices;
+    uint32_t material;
+    uint32_t _pad;
+} rtr_mesh;
+
+/* Volume (lib/volume.rs:19-23): boundary must be a SPHERE or MESH ref; the boundary
+ * object is owned by the volume (it need not appear in `objects`).  neg_inv_density is the
+ * struct's stored field, i.e. -1.0/density as Volume::new computes it (volume.rs:26-31). */
+typedef struct rtr_volume { rtr_object_ref boundary; float neg_inv_density; } rtr_volume;
+
+/* Box<dyn Material> (lib/materials.rs, lib/volume.rs:75-87) */
+enum {
+    RTR_MAT_LAMBERTIAN = 0,  /* color = albedo */
+    RTR_MAT_METAL = 1,       /* color = albedo, param = fuzz */
+    RTR_MAT_EMISSION = 2,    /* color = color*strength, already multiplied (materials.rs:79-83) */
+    RTR_MAT_DIELECTRIC = 3,  /* param = ir */
+    RTR_MAT_MIX = 4,         /* param = factor, first/second = indices into materials[] */
+    RTR_MAT_ISOTROPIC = 5    /* color */
+};
+typedef struct rtr_material {
+    uint32_t kind;
+    rtr_vec3 color;
+    float param;
+    uint32_t first, second;
+} rtr_material;
+
+/* Box<dyn Background> (lib/backgrounds.rs) */
+enum { RTR_BG_UNIFORM = 0, RTR_BG_GRADIENT = 1, RTR_BG_SKYMAP = 2 };
+typedef struct rtr_background {
+    uint32_t kind;
+    rtr_vec3 color;       /* uniform colour | gradient top */
+    rtr_vec3 bottom;      /* gradient bottom */
+    const float* texels;  /* SkyMap.image: RGB f32, row-major, image[x + y*width] */
+    uint32_t width, height;
+} rtr_background;
+
+/* Scene minus camera/settings (lib/core/scene.rs:33-40).  MaterialHandle(i) == materials[i];
+ * children of a MixMaterial are further entries of materials[]. */
+typedef struct rtr_scene_desc {
+    const rtr_object_ref* objects;  /* Scene.objects, in add_object order */
+    const rtr_sphere* spheres;
+    const rtr_mesh* meshes;
+    const rtr_volume* volumes;
+    const rtr_material* materials;
+    uint32_t n_objects, n_spheres, n_meshes, n_volumes, n_materials;
+    uint32_t _pad;
+    rtr_background background;
+} rtr_scene_desc;
+
+/* ---- render ------------------------------------------------------------------- */
+
+enum { RTR_KERNEL_AUTO = 0, RTR_KERNEL_MEGAKERNEL = 1, RTR_KERNEL_WAVEFRONT = 2 };
+enum {
+    RTR_FLAG_EXHAUSTIVE = 1u, /* traverse like the reference: both children, no t-culling */
+    RTR_FLAG_COUNT_WORK = 2u  /* also count nodes / primitive tests / env lookups into rtr_stats */
+};
+
+typedef struct rtr_render_params {
+    uint32_t width, height;  /* RenderTarget.width/height (render.rs:14-19) */
+    rtr_camera camera;       /* Scene.camera */
+    rtr_settings settings;   /* Scene.settings */
+    uint64_t seed;           /* Philox key; the reference is OS-seeded */
+    uint32_t sample_begin;   /* this call renders global samples [begin, begin+count) */
+    uint32_t sample_count;   /* 0 = all of settings.samples_per_pixel */
+    uint32_t kernel;         /* RTR_KERNEL_* */
+    uint32_t flags;          /* RTR_FLAG_* */
+} rtr_render_params;
+
+typedef struct rtr_stats {
+    double device_ms;        /* CUDA events around the render kernels only */
+    double upload_ms;        /* host flatten + H2D, filled by rtr_scene_upload queries */
+    uint64_t rays;           /* world.hit queries (render.rs:38) */
+    uint64_t samples;        /* iterations of render.rs:86 */
+    uint64_t nodes_visited;  /* interior nodes fetched (both child boxes tested) */
+    uint64_t tri_tests;
+    uint64_t sphere_tests;
+    uint64_t env_lookups;    /* SkyMap texel fetches */
+    uint32_t kernel_launches;
+    uint32_t kernel_used;    /* RTR_KERNEL_* actually run */
+} rtr_stats;
+
+/* ---- batch parity entry points -------------------------------------------------- */
+
+typedef struct rtr_ray { rtr_vec3 origin, direction; } rtr_ray;
+
+/* HitRecord<MaterialHandle> (lib/utils/ray.rs:30-36) + which primitive produced it */
+typedef struct rtr_hit {
+    uint32_t object;     /* index into Scene.objects, RTR_NO_HIT on miss */
+    uint32_t primitive;  /* triangle index inside the mesh (original order); 0 otherwise */
+    float t;
+    rtr_vec3 point;
+    rtr_vec3 normal;     /* already front-face flipped */
+    uint32_t front_face;
+    uint32_t material;
+} rtr_hit;
+
+typedef struct rtr_scatter_in {
+    rtr_ray ray;
+    rtr_vec3 point, normal;
+    float t;
+    uint32_t front_face;
+    uint32_t material;
+    uint32_t pixel, sample, bounce;  /* RNG counter for this event */
+} rtr_scatter_in;
+
+typedef struct rtr_scatter_out {
+    rtr_vec3 attenuation;
+    uint32_t scattered;  /* Option<Ray>::is_some */
+    rtr_ray ray;
+} rtr_scatter_out;
+
+typedef struct rtr_context rtr_context;
+typedef struct rtr_scene rtr_scene;
+
+uint32_t rtr_abi_version(void);
+
+/* One context per GPU / per process rank.  stream: a cudaStream_t to launch on, or NULL
+ * for a library-owned stream. */
+rtr_status rtr_context_create(int device, void* stream, rtr_context** out);
+void rtr_context_destroy(rtr_context* ctx);
+const char* rtr_last_error(const rtr_context* ctx); /* ctx may be NULL: last global error */
+
+/* Replaces scene.build_bvh() at render.rs:67 + mesh.build_bvh() (mesh.rs:119-121):
+ * rebuilds the reference BVH topology (bvh.rs:59-144), flattens, uploads once. */
+rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_scene** out);
+void rtr_scene_destroy(rtr_scene* scene);
+/* bytes resident on device / H2D bytes moved by the upload, host build ms */
+rtr_status rtr_scene_info(const rtr_scene* scene, uint64_t* device_bytes, uint64_t* h2d_bytes,
+                          double* build_ms, uint32_t* n_nodes, uint32_t* max_depth);
+
+/* render() (render.rs:61-127).  rgba8_out: host, W*H*4 (may be NULL). accum_out: host,
+ * W*H*4 f32 = per-pixel sum of clamped samples (rgb) + sample count (a) (may be NULL). */
+rtr_status rtr_render(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* params,
+                      uint8_t* rgba8_out, float* accum_out, rtr_stats* stats_out);
+
+/* Multi-GPU building blocks (device pointers; async on the context stream):
+ * accumulate this rank's sample slice into accum_dev (W*H float4, overwritten), then the
+ * caller reduces accum_dev across ranks (one NCCL reduce) and resolves on the root. */
+rtr_status rtr_render_accumulate_device(rtr_context* ctx, const rtr_scene* scene,
+                                        const rtr_render_params* params, float* accum_dev,
+                                        rtr_stats* stats_out);
+/* sqrt(sum/spp) then Color::into_raw (render.rs:103-110, color.rs:34-41) */
+rtr_status rtr_resolve_device(rtr_context* ctx, const float* accum_dev, uint32_t width,
+                              uint32_t height, uint32_t samples_per_pixel, uint8_t* rgba8_dev);
+rtr_status rtr_synchronize(rtr_context* ctx);
+
+/* world.hit(ray, tmin, +INF) for explicit rays (render.rs:38).  Ray i draws any
+ * volume random numbers from counter (pixel=i, sample=0, bounce=0). */
+rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays,
+                           size_t n, float tmin, uint32_t enable_bvh_tree, uint32_t flags,
+                           uint64_t seed, rtr_hit* hits_out, rtr_stats* stats_out);
+/* Material::scatter (materials.rs, volume.rs:82-87); mode FULL or CLAY (render.rs:40-41) */
+rtr_status rtr_scatter_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_scatter_in* in,
+                             size_t n, uint32_t mode, uint64_t seed, rtr_scatter_out* out);
+/* Background::sample (backgrounds.rs:27-29,46-48,85-92): 3 floats per ray */
+rtr_status rtr_background_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays,
+                                size_t n, float* rgb_out);
+/* RayOrigin::get_ray for the jittered sample (pixel, sample) (render.rs:88-92) */
+rtr_status rtr_camera_rays(rtr_context* ctx, const rtr_render_params* params,
+                           const uint32_t* pixels, const uint32_t* samples, size_t n,
+                           rtr_ray* rays_out);
+
+/* ---- host loaders (Scene::from_file scene.rs:74-76, Mesh::from_file mesh.rs:63-76) ---- */
+
+typedef struct rtr_host_scene rtr_host_scene;
+/* Parses the typetag/serde JSON the crate writes; clamp_indirect defaults to 10.0 */
+rtr_status rtr_scene_load_json(const char* path, rtr_host_scene** out);
+const rtr_scene_desc* rtr_host_scene_desc(const rtr_host_scene* hs);
+const rtr_camera* rtr_host_scene_camera(const rtr_host_scene* hs);
+const rtr_settings* rtr_host_scene_settings(const rtr_host_scene* hs);
+void rtr_host_scene_destroy(rtr_host_scene* hs);
+
+typedef struct rtr_host_mesh rtr_host_mesh;
+/* Triangulated OBJ with v//vn or v/vt/vn faces; (position,normal) pairs de-duplicated */
+rtr_status rtr_mesh_load_obj(const char* path, uint32_t material, rtr_host_mesh** out);
+const rtr_mesh* rtr_host_mesh_get(const rtr_host_mesh* hm);
+void rtr_host_mesh_destroy(rtr_host_mesh* hm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTR_H_ */

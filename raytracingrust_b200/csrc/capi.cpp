@@ -1,0 +1,474 @@
+// capi.cpp — implementation of the C ABI declared in include/rtr.h.
+//
+// No CPU fallback exists: every entry point that computes launches CUDA kernels (kernels.cu)
+// and returns RTR_CUDA_ERROR when no device is usable.
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/rtr.h"
+#include "host_flatten.h"
+#include "kernels.h"
+
+using namespace rtr;
+
+static std::string g_last_error;
+static std::mutex g_err_mu;
+
+struct rtr_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    uint32_t* work_counter = nullptr;
+    unsigned long long* stats = nullptr;  // STAT_COUNT
+    // scratch, grown on demand
+    float4* accum = nullptr; size_t accum_pixels = 0;
+    float4* partials = nullptr; size_t partials_elems = 0;
+    uchar4* rgba = nullptr; size_t rgba_pixels = 0;
+    char* batch_in = nullptr; size_t batch_in_bytes = 0;
+    char* batch_in2 = nullptr; size_t batch_in2_bytes = 0;
+    char* batch_out = nullptr; size_t batch_out_bytes = 0;
+    std::string error;
+};
+
+struct rtr_scene {
+    rtr_context* ctx = nullptr;
+    SceneView view;
+    std::vector<void*> allocs;
+    uint64_t device_bytes = 0, h2d_bytes = 0;
+    double build_ms = 0.0;
+    uint32_t n_nodes = 0, max_depth = 0;
+};
+
+static rtr_status fail(rtr_context* ctx, rtr_status st, const std::string& msg) {
+    if (ctx) ctx->error = msg;
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    g_last_error = msg;
+    return st;
+}
+namespace rtr { void set_global_error(const std::string& m) { fail(nullptr, RTR_OK, m); } }
+static rtr_status cuda_fail(rtr_context* ctx, cudaError_t e, const char* what) {
+    return fail(ctx, e == cudaErrorMemoryAllocation ? RTR_OOM : RTR_CUDA_ERROR,
+                std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                                  \
+    do {                                                          \
+        cudaError_t e_ = (call);                                  \
+        if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call);  \
+    } while (0)
+
+template <typename T>
+static cudaError_t grow(T** p, size_t* have, size_t want) {
+    if (*have >= want && *p) return cudaSuccess;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *have = 0;
+    cudaError_t e = cudaMalloc((void**)p, want * sizeof(T));
+    if (e == cudaSuccess) *have = want;
+    return e;
+}
+
+// ------------------------------------------------------------------ camera (camera.rs:37-56)
+// host f32 arithmetic in the reference's order (this TU is built with -ffp-contract=off)
+namespace {
+inline v3 vsub(v3 a, v3 b) { return v3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline v3 vadd(v3 a, v3 b) { return v3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline v3 vscale(float s, v3 a) { return v3{s * a.x, s * a.y, s * a.z}; }
+inline v3 vdiv(v3 a, float s) { return v3{a.x / s, a.y / s, a.z / s}; }
+inline float vdot(v3 a, v3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline v3 vcross(v3 a, v3 b) { return v3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline v3 vnormalize(v3 a) { float s = 1.0f / std::sqrt(vdot(a, a)); return v3{a.x * s, a.y * s, a.z * s}; }
+inline v3 from(const rtr_vec3& v) { return v3{v.x, v.y, v.z}; }
+
+CameraBasis ray_origin(const rtr_camera& cam) {
+    const float PI = 3.14159265358979323846f;
+    float theta = cam.vertical_fov * PI / 180.0f;  // degrees_to_radians (math.rs:32-34)
+    float h = std::tan(theta / 2.0f);
+    float viewport_height = 2.0f * h;
+    float viewport_width = cam.aspect_ratio * viewport_height;
+    v3 w = vnormalize(vsub(from(cam.lookfrom), from(cam.lookat)));
+    v3 u = vnormalize(vcross(from(cam.vertical), w));
+    v3 v = vcross(w, u);
+    v3 horizontal = vscale(viewport_width, u);
+    v3 vertical = vscale(viewport_height, v);
+    CameraBasis b;
+    b.origin = from(cam.lookfrom);
+    b.horizontal = horizontal;
+    b.vertical = vertical;
+    b.lower_left_corner = vsub(vadd(vsub(from(cam.lookfrom), vdiv(horizontal, 2.0f)), vdiv(vertical, 2.0f)), w);
+    return b;
+}
+}  // namespace
+
+extern "C" {
+
+uint32_t rtr_abi_version(void) { return RTR_ABI_VERSION; }
+
+const char* rtr_last_error(const rtr_context* ctx) {
+    if (ctx) return ctx->error.c_str();
+    return g_last_error.c_str();
+}
+
+rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
+    if (!out) return fail(nullptr, RTR_INVALID_ARG, "rtr_context_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, RTR_CUDA_ERROR, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                                 " (this library has no CPU fallback)");
+    if (device < 0 || device >= n) return fail(nullptr, RTR_INVALID_ARG, "rtr_context_create: bad device index");
+    rtr_context* ctx = new (std::nothrow) rtr_context();
+    if (!ctx) return fail(nullptr, RTR_OOM, "host allocation failed");
+    ctx->device = device;
+    CU(cudaSetDevice(device));
+    if (stream) { ctx->stream = (cudaStream_t)stream; ctx->own_stream = false; }
+    else { CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
+    CU(cudaEventCreate(&ctx->ev0));
+    CU(cudaEventCreate(&ctx->ev1));
+    CU(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+    CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
+    CU(cudaMalloc((void**)&ctx->stats, STAT_COUNT * sizeof(unsigned long long)));
+    *out = ctx;
+    return RTR_OK;
+}
+
+void rtr_context_destroy(rtr_context* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->work_counter); cudaFree(ctx->stats); cudaFree(ctx->accum); cudaFree(ctx->partials);
+    cudaFree(ctx->rgba); cudaFree(ctx->batch_in); cudaFree(ctx->batch_in2); cudaFree(ctx->batch_out);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+rtr_status rtr_synchronize(rtr_context* ctx) {
+    if (!ctx) return fail(nullptr, RTR_INVALID_ARG, "null context");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RTR_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ scene upload
+template <typename T>
+static cudaError_t upload(rtr_scene* s, const std::vector<T>& v, const T** dst, cudaStream_t st) {
+    *dst = nullptr;
+    size_t bytes = v.size() * sizeof(T);
+    if (bytes == 0) bytes = sizeof(T);  // keep pointers valid
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return e;
+    s->allocs.push_back(p);
+    s->device_bytes += bytes;
+    if (!v.empty()) {
+        e = cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+        s->h2d_bytes += v.size() * sizeof(T);
+    }
+    *dst = (const T*)p;
+    return e;
+}
+
+extern "C" {
+
+rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_scene** out) {
+    if (!ctx || !desc || !out) return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: null argument");
+    *out = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    auto t0 = std::chrono::steady_clock::now();
+    HostFlat flat;
+    std::string err;
+    int rc = RTR_OK;
+    try {
+        rc = flatten_scene(*desc, flat, err);
+    } catch (const std::bad_alloc&) {
+        return fail(ctx, RTR_OOM, "host allocation failed while flattening");
+    }
+    if (rc != RTR_OK) return fail(ctx, (rtr_status)rc, "rtr_scene_upload: " + err);
+    const uint32_t need = flat.max_depth + flat.max_boundary_depth + 2;
+    if (need > 48)  // RTR_STACK_CAP
+        return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack");
+    auto t1 = std::chrono::steady_clock::now();
+    rtr_scene* s = new (std::nothrow) rtr_scene();
+    if (!s) return fail(ctx, RTR_OOM, "host allocation failed");
+    s->ctx = ctx;
+    s->build_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+    s->n_nodes = (uint32_t)(flat.nodes.size() / 4);
+    s->max_depth = flat.max_depth;
+    SceneView& v = s->view;
+    std::memset(&v, 0, sizeof(v));
+    cudaError_t e = cudaSuccess;
+    auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
+    step(upload(s, flat.nodes, &v.nodes, ctx->stream));
+    step(upload(s, flat.spheres, &v.spheres, ctx->stream));
+    step(upload(s, flat.sphere_info, &v.sphere_info, ctx->stream));
+    step(upload(s, flat.tris, &v.tris, ctx->stream));
+    step(upload(s, flat.tri_vn, &v.tri_vn, ctx->stream));
+    step(upload(s, flat.tri_info, &v.tri_info, ctx->stream));
+    step(upload(s, flat.volumes, &v.volumes, ctx->stream));
+    step(upload(s, flat.objects, &v.objects, ctx->stream));
+    step(upload(s, flat.materials, &v.materials, ctx->stream));
+    step(upload(s, flat.env, &v.env, ctx->stream));
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // host vectors die at return
+    if (e != cudaSuccess) {
+        rtr_scene_destroy(s);
+        return cuda_fail(ctx, e, "rtr_scene_upload");
+    }
+    v.background = flat.background;
+    v.root_entry = flat.root_entry;
+    v.n_objects = (uint32_t)flat.objects.size();
+    v.n_materials = (uint32_t)flat.materials.size();
+    v.n_volumes = (uint32_t)flat.volumes.size();
+    *out = s;
+    return RTR_OK;
+}
+
+void rtr_scene_destroy(rtr_scene* s) {
+    if (!s) return;
+    if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
+    for (void* p : s->allocs) cudaFree(p);
+    delete s;
+}
+
+rtr_status rtr_scene_info(const rtr_scene* s, uint64_t* device_bytes, uint64_t* h2d_bytes, double* build_ms,
+                          uint32_t* n_nodes, uint32_t* max_depth) {
+    if (!s) return fail(nullptr, RTR_INVALID_ARG, "null scene");
+    if (device_bytes) *device_bytes = s->device_bytes;
+    if (h2d_bytes) *h2d_bytes = s->h2d_bytes;
+    if (build_ms) *build_ms = s->build_ms;
+    if (n_nodes) *n_nodes = s->n_nodes;
+    if (max_depth) *max_depth = s->max_depth;
+    return RTR_OK;
+}
+
+// ------------------------------------------------------------------ render
+static rtr_status check_render_args(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p) {
+    if (!ctx || !scene || !p) return fail(ctx, RTR_INVALID_ARG, "render: null argument");
+    if (scene->ctx != ctx) return fail(ctx, RTR_INVALID_ARG, "render: scene belongs to another context");
+    if (p->settings.max_ray_depth > 255) return fail(ctx, RTR_INVALID_ARG, "max_ray_depth is a u8 in the reference");
+    if (p->settings.mode > RTR_MODE_NORMAL) return fail(ctx, RTR_INVALID_ARG, "unknown render mode");
+    if (p->kernel > RTR_KERNEL_WAVEFRONT) return fail(ctx, RTR_INVALID_ARG, "unknown kernel selector");
+    if ((uint64_t)p->width * p->height > 0x7FFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "image too large");
+    const uint32_t spp = p->settings.samples_per_pixel;
+    const uint32_t cnt = p->sample_count ? p->sample_count : spp;
+    if ((uint64_t)p->sample_begin + cnt > 0xFFFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "sample range overflows u32");
+    return RTR_OK;
+}
+
+// launches the render kernels for this call's sample slice into accum_dev; fills stats (async)
+static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
+                              float4* accum_dev, bool timed, rtr_stats* stats_out) {
+    const uint32_t W = p->width, H = p->height;
+    const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
+    const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;
+    const bool count_work = stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0;
+    RenderArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.sc = scene->view;
+    a.cam = ray_origin(p->camera);
+    a.width = W; a.height = H;
+    a.max_ray_depth = p->settings.max_ray_depth;
+    a.clamp_indirect = p->settings.clamp_indirect;
+    a.enable_bvh_tree = p->settings.enable_bvh_tree;
+    a.mode = p->settings.mode;
+    a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
+    a.sample_begin = p->sample_begin; a.sample_count = count;
+    a.tiles_x = (W + 7) / 8;
+    a.n_tiles = a.tiles_x * ((H + 3) / 4);
+    // persistent grid: one block per resident slot
+    int per_sm = megakernel_max_blocks_per_sm(exhaustive, count_work);
+    if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "megakernel cannot be resident on this device");
+    const uint32_t resident_warps = (uint32_t)ctx->sm_count * per_sm * (RTR_MEGA_THREADS / 32);
+    // small image + many samples: split the samples of a tile into chunks so the chip is full
+    a.n_chunks = 1; a.chunk_samples = count ? count : 1;
+    if (a.n_tiles < 4 * resident_warps && count > 1) {
+        uint32_t want = (4 * resident_warps + a.n_tiles - 1) / (a.n_tiles ? a.n_tiles : 1);
+        if (want > count) want = count;
+        a.chunk_samples = (count + want - 1) / want;
+        a.n_chunks = (count + a.chunk_samples - 1) / a.chunk_samples;
+    }
+    a.accum = accum_dev;
+    if (a.n_chunks > 1) {
+        CU(grow(&ctx->partials, &ctx->partials_elems, (size_t)a.n_chunks * W * H));
+        a.partials = ctx->partials;
+    }
+    a.work_counter = ctx->work_counter;
+    a.stats = ctx->stats;
+    CU(cudaMemsetAsync(ctx->work_counter, 0, sizeof(uint32_t), ctx->stream));
+    CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
+    uint32_t launches = 0;
+    if (timed) CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (W && H) {
+        uint32_t items = a.n_tiles * a.n_chunks;
+        uint32_t blocks = (uint32_t)ctx->sm_count * per_sm;
+        uint32_t need_blocks = (items + (RTR_MEGA_THREADS / 32) - 1) / (RTR_MEGA_THREADS / 32);
+        if (blocks > need_blocks) blocks = need_blocks;
+        CU(launch_megakernel(a, (int)blocks, exhaustive, count_work, ctx->stream));
+        ++launches;
+        if (a.n_chunks > 1) {
+            CU(launch_sum_chunks(a.partials, accum_dev, W * H, a.n_chunks, ctx->stream));
+            ++launches;
+        }
+    }
+    if (timed) CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    if (stats_out) {
+        std::memset(stats_out, 0, sizeof(*stats_out));
+        stats_out->kernel_launches = launches;
+        stats_out->kernel_used = RTR_KERNEL_MEGAKERNEL;
+        stats_out->samples = (uint64_t)W * H * count;
+    }
+    return RTR_OK;
+}
+
+static rtr_status collect_stats(rtr_context* ctx, bool timed, rtr_stats* stats_out) {
+    if (!stats_out) return RTR_OK;
+    unsigned long long h[STAT_COUNT];
+    CU(cudaMemcpyAsync(h, ctx->stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    stats_out->rays = h[STAT_RAYS]; stats_out->nodes_visited = h[STAT_NODES]; stats_out->tri_tests = h[STAT_TRIS];
+    stats_out->sphere_tests = h[STAT_SPHERES]; stats_out->env_lookups = h[STAT_ENV];
+    if (timed) {
+        float ms = 0.0f;
+        CU(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        stats_out->device_ms = ms;
+    }
+    return RTR_OK;
+}
+
+rtr_status rtr_render(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p, uint8_t* rgba8_out,
+                      float* accum_out, rtr_stats* stats_out) {
+    rtr_status st = check_render_args(ctx, scene, p);
+    if (st != RTR_OK) return st;
+    CU(cudaSetDevice(ctx->device));
+    const size_t n = (size_t)p->width * p->height;
+    if (n == 0) { if (stats_out) std::memset(stats_out, 0, sizeof(*stats_out)); return RTR_OK; }
+    CU(grow(&ctx->accum, &ctx->accum_pixels, n));
+    CU(grow(&ctx->rgba, &ctx->rgba_pixels, n));
+    st = render_into(ctx, scene, p, ctx->accum, true, stats_out);
+    if (st != RTR_OK) return st;
+    const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
+    if (rgba8_out) {
+        CU(launch_resolve(ctx->accum, ctx->rgba, (uint32_t)n, (float)count, ctx->stream));
+        if (stats_out) stats_out->kernel_launches++;
+        CU(cudaMemcpyAsync(rgba8_out, ctx->rgba, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (accum_out) CU(cudaMemcpyAsync(accum_out, ctx->accum, n * sizeof(float4), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return collect_stats(ctx, true, stats_out);
+}
+
+rtr_status rtr_render_accumulate_device(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
+                                        float* accum_dev, rtr_stats* stats_out) {
+    rtr_status st = check_render_args(ctx, scene, p);
+    if (st != RTR_OK) return st;
+    if (!accum_dev) return fail(ctx, RTR_INVALID_ARG, "accum_dev is NULL");
+    CU(cudaSetDevice(ctx->device));
+    st = render_into(ctx, scene, p, (float4*)accum_dev, stats_out != nullptr, stats_out);
+    if (st != RTR_OK) return st;
+    return collect_stats(ctx, true, stats_out);  // synchronises only when stats are requested
+}
+
+rtr_status rtr_resolve_device(rtr_context* ctx, const float* accum_dev, uint32_t width, uint32_t height,
+                              uint32_t samples_per_pixel, uint8_t* rgba8_dev) {
+    if (!ctx || !accum_dev || !rgba8_dev) return fail(ctx, RTR_INVALID_ARG, "rtr_resolve_device: null argument");
+    CU(cudaSetDevice(ctx->device));
+    if ((uint64_t)width * height == 0) return RTR_OK;
+    CU(launch_resolve((const float4*)accum_dev, (uchar4*)rgba8_dev, width * height, (float)samples_per_pixel, ctx->stream));
+    return RTR_OK;
+}
+
+// ------------------------------------------------------------------ batch entry points
+rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays, size_t n, float tmin,
+                           uint32_t enable_bvh_tree, uint32_t flags, uint64_t seed, rtr_hit* hits_out,
+                           rtr_stats* stats_out) {
+    if (!ctx || !scene || (n && (!rays || !hits_out))) return fail(ctx, RTR_INVALID_ARG, "rtr_trace_batch: null argument");
+    if (scene->ctx != ctx) return fail(ctx, RTR_INVALID_ARG, "scene belongs to another context");
+    if (stats_out) std::memset(stats_out, 0, sizeof(*stats_out));
+    if (n == 0) return RTR_OK;
+    if (n > 0xFFFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "batch too large (ray index is the u32 RNG counter)");
+    CU(cudaSetDevice(ctx->device));
+    CU(grow(&ctx->batch_in, &ctx->batch_in_bytes, n * sizeof(rtr_ray)));
+    CU(grow(&ctx->batch_out, &ctx->batch_out_bytes, n * sizeof(rtr_hit)));
+    CU(cudaMemcpyAsync(ctx->batch_in, rays, n * sizeof(rtr_ray), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    CU(launch_trace_batch(scene->view, (const rtr_ray*)ctx->batch_in, n, tmin, enable_bvh_tree,
+                          (flags & RTR_FLAG_EXHAUSTIVE) != 0, (uint32_t)seed, (uint32_t)(seed >> 32),
+                          (rtr_hit*)ctx->batch_out, ctx->stats, ctx->stream));
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    CU(cudaMemcpyAsync(hits_out, ctx->batch_out, n * sizeof(rtr_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (stats_out) {
+        stats_out->rays = n; stats_out->kernel_launches = 1; stats_out->kernel_used = RTR_KERNEL_MEGAKERNEL;
+        rtr_status st = collect_stats(ctx, true, stats_out);
+        stats_out->rays = n;
+        return st;
+    }
+    return RTR_OK;
+}
+
+rtr_status rtr_scatter_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_scatter_in* in, size_t n,
+                             uint32_t mode, uint64_t seed, rtr_scatter_out* out) {
+    if (!ctx || !scene || (n && (!in || !out))) return fail(ctx, RTR_INVALID_ARG, "rtr_scatter_batch: null argument");
+    if (scene->ctx != ctx) return fail(ctx, RTR_INVALID_ARG, "scene belongs to another context");
+    if (mode != RTR_MODE_FULL && mode != RTR_MODE_CLAY) return fail(ctx, RTR_INVALID_ARG, "scatter mode must be FULL or CLAY");
+    if (n == 0) return RTR_OK;
+    if (mode == RTR_MODE_FULL)
+        for (size_t i = 0; i < n; ++i)
+            if (in[i].material >= scene->view.n_materials) return fail(ctx, RTR_INVALID_ARG, "material handle out of range");
+    CU(cudaSetDevice(ctx->device));
+    CU(grow(&ctx->batch_in, &ctx->batch_in_bytes, n * sizeof(rtr_scatter_in)));
+    CU(grow(&ctx->batch_out, &ctx->batch_out_bytes, n * sizeof(rtr_scatter_out)));
+    CU(cudaMemcpyAsync(ctx->batch_in, in, n * sizeof(rtr_scatter_in), cudaMemcpyHostToDevice, ctx->stream));
+    CU(launch_scatter_batch(scene->view, (const rtr_scatter_in*)ctx->batch_in, n, mode, (uint32_t)seed,
+                            (uint32_t)(seed >> 32), (rtr_scatter_out*)ctx->batch_out, ctx->stream));
+    CU(cudaMemcpyAsync(out, ctx->batch_out, n * sizeof(rtr_scatter_out), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RTR_OK;
+}
+
+rtr_status rtr_background_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays, size_t n,
+                                float* rgb_out) {
+    if (!ctx || !scene || (n && (!rays || !rgb_out))) return fail(ctx, RTR_INVALID_ARG, "rtr_background_batch: null argument");
+    if (scene->ctx != ctx) return fail(ctx, RTR_INVALID_ARG, "scene belongs to another context");
+    if (n == 0) return RTR_OK;
+    CU(cudaSetDevice(ctx->device));
+    CU(grow(&ctx->batch_in, &ctx->batch_in_bytes, n * sizeof(rtr_ray)));
+    CU(grow(&ctx->batch_out, &ctx->batch_out_bytes, n * 3 * sizeof(float)));
+    CU(cudaMemcpyAsync(ctx->batch_in, rays, n * sizeof(rtr_ray), cudaMemcpyHostToDevice, ctx->stream));
+    CU(launch_background_batch(scene->view, (const rtr_ray*)ctx->batch_in, n, (float*)ctx->batch_out, ctx->stream));
+    CU(cudaMemcpyAsync(rgb_out, ctx->batch_out, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RTR_OK;
+}
+
+rtr_status rtr_camera_rays(rtr_context* ctx, const rtr_render_params* p, const uint32_t* pixels,
+                           const uint32_t* samples, size_t n, rtr_ray* rays_out) {
+    if (!ctx || !p || (n && (!pixels || !samples || !rays_out))) return fail(ctx, RTR_INVALID_ARG, "rtr_camera_rays: null argument");
+    if (p->width == 0 || p->height == 0) return fail(ctx, RTR_INVALID_ARG, "empty render target");
+    if (n == 0) return RTR_OK;
+    CU(cudaSetDevice(ctx->device));
+    CU(grow(&ctx->batch_in, &ctx->batch_in_bytes, n * sizeof(uint32_t)));
+    CU(grow(&ctx->batch_in2, &ctx->batch_in2_bytes, n * sizeof(uint32_t)));
+    CU(grow(&ctx->batch_out, &ctx->batch_out_bytes, n * sizeof(rtr_ray)));
+    CU(cudaMemcpyAsync(ctx->batch_in, pixels, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(ctx->batch_in2, samples, n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    CU(launch_camera_rays(ray_origin(p->camera), p->width, p->height, (uint32_t)p->seed, (uint32_t)(p->seed >> 32),
+                          (const uint32_t*)ctx->batch_in, (const uint32_t*)ctx->batch_in2, n, (rtr_ray*)ctx->batch_out,
+                          ctx->stream));
+    CU(cudaMemcpyAsync(rays_out, ctx->batch_out, n * sizeof(rtr_ray), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return RTR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,473 @@
+// device_core.cuh — device routines of the render hot path (sm_100a).
+//
+// Every arithmetic expression below reproduces the reference's f32 evaluation order so that,
+// compiled with -fmad=false (no FMA contraction; Rust never contracts), -prec-div=true and
+// -prec-sqrt=true (nvcc defaults), results are bit-identical to the CPU oracle except for
+// logf/acosf/atan2f (CUDA libm vs glibc, <= 2 ulp).  Reference citations are file:line.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rtr.h"
+#include "flat.h"
+#include "kernels.h"
+
+namespace rtr {
+
+#define RTR_INF __int_as_float(0x7f800000)
+#define RTR_PI 3.14159265358979323846f  // std::f32::consts::PI (types.rs:5)
+#define RTR_STACK_CAP 48                // (ref, enter) pairs per thread; host checks max depth
+
+// ------------------------------------------------------------------ vectors (cgmath 0.18 order)
+// struct v3 { float x, y, z; } comes from kernels.h
+__device__ __forceinline__ v3 mk(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ v3 operator+(v3 a, v3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ v3 operator-(v3 a, v3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ v3 operator-(v3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ v3 operator*(v3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ v3 operator*(float s, v3 a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ v3 operator*(v3 a, v3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ v3 operator/(v3 a, float s) { return mk(a.x / s, a.y / s, a.z / s); }
+__device__ __forceinline__ float dot(v3 a, v3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+__device__ __forceinline__ v3 cross(v3 a, v3 b) {
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ float magnitude(v3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ v3 normalize(v3 a) { return a * (1.0f / magnitude(a)); }
+__device__ __forceinline__ v3 xyz(const float4& q) { return mk(q.x, q.y, q.z); }
+
+struct Ray { v3 o, d; };
+__device__ __forceinline__ v3 ray_at(const Ray& r, float t) { return r.o + r.d * t; }  // ray.rs:15-17
+
+__device__ __forceinline__ float4 ldg4(const F4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ uint4 ldgu4(const U4* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// ------------------------------------------------------------------ Philox4x32-10, keyed draws
+__device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                               uint32_t k0, uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        uint32_t h0 = __umulhi(M0, c0), l0 = M0 * c0;
+        uint32_t h1 = __umulhi(M1, c2), l1 = M1 * c2;
+        uint32_t n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += W0; k1 += W1;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+enum { P_JITTER = 0, P_SPHERE = 1, P_MIX = 2, P_DIELECTRIC = 3, P_VOLUME = 4 };
+
+struct RngKey { uint32_t k0, k1, pixel, sample, bounce; };
+__device__ __forceinline__ uint4 draw(const RngKey& k, uint32_t purpose, uint32_t iter) {
+    return philox4x32_10(k.pixel, k.sample, (k.bounce & 0xFFu) | (purpose << 8), iter, k.k0, k.k1);
+}
+// rand 0.8 UniformFloat<f32>: 23 mantissa bits -> [0,1)
+__device__ __forceinline__ float u01(uint32_t b) { return (float)(b >> 9) * (1.0f / 8388608.0f); }
+__device__ __forceinline__ float gen_range_01(uint32_t b) { return u01(b); }
+__device__ __forceinline__ float gen_range_m11(uint32_t b) { return u01(b) * 2.0f + -1.0f; }
+__device__ __forceinline__ float gen_range_01_inclusive(uint32_t b) {
+    const float scale = 1.0f / (1.0f - 1.0f / 8388608.0f);
+    return u01(b) * scale + 0.0f;
+}
+// sample.rs:44-52
+__device__ __forceinline__ v3 sample_unit_sphere_volume(const RngKey& key) {
+    for (uint32_t k = 0;; ++k) {
+        uint4 r = draw(key, P_SPHERE, k);
+        v3 v = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
+        if (dot(v, v) <= 1.0f) return v;
+    }
+}
+__device__ __forceinline__ v3 sample_unit_sphere_surface(const RngKey& key) {  // sample.rs:66-70
+    return normalize(sample_unit_sphere_volume(key));
+}
+
+// ------------------------------------------------------------------ work counters (optional)
+struct Counters { uint32_t nodes, tris, spheres, env; };
+
+// ------------------------------------------------------------------ AABB::hit (aabb.rs:81-137)
+// Same t0/t1/swap/update sequence; the per-axis early-outs are folded into the final test, which
+// is equivalent because tmin only grows and tmax only shrinks.  inv = 1/d is hoisted per ray
+// (same IEEE quotient the reference recomputes at every node).  Returns pierced; enter = final tmin.
+struct RayInv { float ix, iy, iz; };
+__device__ __forceinline__ bool slab(const float4& mn, const float4& mx, const Ray& r, const RayInv& inv,
+                                     float tmin, float& enter) {
+    float tmax = RTR_INF;
+    float t0 = (mn.x - r.o.x) * inv.ix, t1 = (mx.x - r.o.x) * inv.ix;
+    if (inv.ix < 0.0f) { float s = t0; t0 = t1; t1 = s; }
+    if (t0 > tmin) tmin = t0;
+    if (t1 < tmax) tmax = t1;
+    t0 = (mn.y - r.o.y) * inv.iy; t1 = (mx.y - r.o.y) * inv.iy;
+    if (inv.iy < 0.0f) { float s = t0; t0 = t1; t1 = s; }
+    if (t0 > tmin) tmin = t0;
+    if (t1 < tmax) tmax = t1;
+    t0 = (mn.z - r.o.z) * inv.iz; t1 = (mx.z - r.o.z) * inv.iz;
+    if (inv.iz < 0.0f) { float s = t0; t0 = t1; t1 = s; }
+    if (t0 > tmin) tmin = t0;
+    if (t1 < tmax) tmax = t1;
+    enter = tmin;
+    return !(tmax <= tmin);
+}
+
+// ------------------------------------------------------------------ primitives
+// Sphere::hit (objects.rs:23-50), t only; point/normal are rebuilt for the winner in finish_hit
+__device__ __forceinline__ bool sphere_t(const float4& s, const Ray& r, float tmin, float tmax, float& t) {
+    v3 oc = r.o - xyz(s);
+    float a = dot(r.d, r.d);
+    float half_b = dot(oc, r.d);
+    float c = dot(oc, oc) - s.w * s.w;
+    float disc = half_b * half_b - a * c;
+    if (disc < 0.0f) return false;
+    float sqrtd = sqrtf(disc);
+    float root = (-half_b - sqrtd) / a;
+    if (root < tmin || tmax < root) {
+        root = (-half_b + sqrtd) / a;
+        if (root < tmin || tmax < root) return false;
+    }
+    t = root;
+    return true;
+}
+
+// Triangle::hit (mesh.rs:147-196): tmin doubles as the determinant epsilon (Q4); tmax ignored
+__device__ __forceinline__ bool triangle_t(const float4& q0, const float4& q1, const float4& q2, const Ray& r,
+                                           float tmin, float& t, float& u, float& v) {
+    v3 e1 = xyz(q1), e2 = xyz(q2);
+    v3 h = cross(r.d, e2);
+    float a = dot(e1, h);
+    if (a > -tmin && a < tmin) return false;
+    float f = 1.0f / a;
+    v3 s = r.o - xyz(q0);
+    u = f * dot(s, h);
+    if (u < 0.0f || u > 1.0f) return false;
+    v3 q = cross(s, e1);
+    v = f * dot(r.d, q);
+    if (v < 0.0f || u + v > 1.0f) return false;
+    t = f * dot(e2, q);
+    return t > tmin;
+}
+
+struct LiteHit {
+    float t;
+    uint32_t ref;  // REF_EMPTY_VALUE = miss
+    float u, v;    // barycentrics of a triangle winner
+};
+
+// candidate update: min t; among equal t the larger DFS leaf rank wins (bvh.rs:183-187, Q2)
+__device__ __forceinline__ uint32_t leaf_rank(const SceneView& sc, uint32_t ref) {
+    uint32_t k = RTR_REF_KIND(ref), i = RTR_REF_INDEX(ref);
+    if (k == REF_SPHERE) return __ldg(&sc.sphere_info[i].w);
+    if (k == REF_TRI) return __ldg(&sc.tri_info[i].w);
+    return sc.volumes[i].rank;
+}
+__device__ __forceinline__ void offer(const SceneView& sc, LiteHit& best, float t, uint32_t ref, float u, float v) {
+    bool take = t < best.t;
+    if (!take && t == best.t) take = best.ref == REF_EMPTY_VALUE || leaf_rank(sc, ref) > leaf_rank(sc, best.ref);
+    if (take) { best.t = t; best.ref = ref; best.u = u; best.v = v; }
+}
+
+// t-culling threshold.  A subtree is skipped when its box entry lies beyond the current best by
+// more than this slack; the slack absorbs the few-ulp (sphere quadratic: worse) disagreement
+// between a primitive's computed t and its box's computed entry.  RTR_FLAG_EXHAUSTIVE disables
+// culling altogether (reference-shaped walk) and is used to validate the culled walk at scale.
+__device__ __forceinline__ float cull_limit(float best_t) {
+    return best_t + fmaxf(fabsf(best_t) * (1.0f / 256.0f), 1.0e-6f);
+}
+
+struct StackEntry { uint32_t ref; float enter; };
+
+// Closest hit below `entry` for (tmin, +INF).  NESTED = a volume boundary / mesh sub-query:
+// volume leaves cannot occur there.  Volume leaves of the outer walk are handled by the caller
+// through `on_volume`.
+__device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+                            float tmin, float tmax, const RngKey& key, StackEntry* stack, bool exhaustive,
+                            Counters* cnt);
+
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
+__device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const Ray& r, const RayInv& inv,
+                                     float tmin, const RngKey& key, StackEntry* stack, LiteHit& best,
+                                     Counters* cnt) {
+    uint32_t cur = entry;
+    int sp = 0;
+    for (;;) {
+        const uint32_t kind = RTR_REF_KIND(cur);
+        if (kind == REF_NODE) {
+            const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
+            const float4 q0 = ldg4(q), q1 = ldg4(q + 1), q2 = ldg4(q + 2), q3 = ldg4(q + 3);
+            if (COUNT) cnt->nodes++;
+            uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
+            float le = -RTR_INF, re = -RTR_INF;
+            bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
+            if (RTR_REF_KIND(lref) == REF_NODE) lh = slab(q0, q1, r, inv, tmin, le);
+            if (RTR_REF_KIND(rref) == REF_NODE) rh = slab(q2, q3, r, inv, tmin, re);
+            if (!EXHAUSTIVE) {
+                const float lim = cull_limit(best.t);
+                lh = lh && !(le > lim);
+                rh = rh && !(re > lim);
+            }
+            if (lh && rh) {
+                if (re < le) { uint32_t tr = lref; lref = rref; rref = tr; float te = le; le = re; re = te; }
+                stack[sp].ref = rref; stack[sp].enter = re; ++sp;
+                cur = lref;
+                continue;
+            }
+            if (lh) { cur = lref; continue; }
+            if (rh) { cur = rref; continue; }
+        } else if (kind == REF_SPHERE) {
+            const uint32_t i = RTR_REF_INDEX(cur);
+            float t;
+            if (COUNT) cnt->spheres++;
+            if (sphere_t(ldg4(sc.spheres + i), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
+        } else if (kind == REF_TRI) {
+            const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 3;
+            float t, u, v;
+            if (COUNT) cnt->tris++;
+            if (triangle_t(ldg4(q), ldg4(q + 1), ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
+        } else if (!NESTED && kind == REF_VOLUME) {
+            const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
+            float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack + sp, EXHAUSTIVE, COUNT ? cnt : nullptr);
+            if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
+        }
+        // pop
+        for (;;) {
+            if (sp == 0) return;
+            --sp;
+            cur = stack[sp].ref;
+            if (EXHAUSTIVE || !(stack[sp].enter > cull_limit(best.t))) break;
+        }
+    }
+}
+
+// boundary.hit(ray, tmin, +INF) of a volume boundary: only t is consumed (volume.rs:36-37)
+__device__ __forceinline__ bool boundary_t(const SceneView& sc, uint32_t entry, const Ray& r, const RayInv& inv,
+                                           float tmin, StackEntry* stack, bool exhaustive, Counters* cnt, float& t) {
+    LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+    RngKey nokey; nokey.k0 = nokey.k1 = nokey.pixel = nokey.sample = nokey.bounce = 0;
+    Counters dummy; dummy.nodes = dummy.tris = dummy.spheres = dummy.env = 0;
+    Counters* c = cnt ? cnt : &dummy;
+    if (exhaustive) walk<true, true, true>(sc, entry, r, inv, tmin, nokey, stack, best, c);
+    else walk<false, true, true>(sc, entry, r, inv, tmin, nokey, stack, best, c);
+    t = best.t;
+    return best.ref != REF_EMPTY_VALUE;
+}
+
+// Volume::hit (volume.rs:35-72).  Returns t, or NaN for None.
+__device__ __noinline__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+                                         float tmin, float tmax, const RngKey& key, StackEntry* stack,
+                                         bool exhaustive, Counters* cnt) {
+    const float NONE = __int_as_float(0x7fc00000);
+    float t1, t2;
+    if (!boundary_t(sc, vol.entry, r, inv, -RTR_INF, stack, exhaustive, cnt, t1)) return NONE;
+    if (!boundary_t(sc, vol.entry, r, inv, t1 + tmin, stack, exhaustive, cnt, t2)) return NONE;
+    if (t1 < tmin) t1 = tmin;
+    if (t2 > tmax) t2 = tmax;
+    if (t1 >= t2) return NONE;
+    if (t1 < 0.0f) t1 = 0.0f;
+    float ray_length = magnitude(r.d);
+    float distance_inside_boundary = (t2 - t1) * ray_length;
+    float random_float = gen_range_01_inclusive(draw(key, P_VOLUME, vol.index).x);  // volume.rs:57
+    float hit_distance = vol.neg_inv_density * logf(random_float);
+    if (hit_distance > distance_inside_boundary) return NONE;
+    return t1 + hit_distance / ray_length;
+}
+
+// world.hit(ray, tmin, +INF) with the BVH (bvh.rs:47-49) or the linear scan (scene.rs:141-156)
+template <bool EXHAUSTIVE, bool COUNT>
+__device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, const Ray& r, float tmin,
+                                             const RngKey& key, StackEntry* stack, Counters* cnt) {
+    RayInv inv; inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z;
+    LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+    if (bvh) {
+        walk<EXHAUSTIVE, COUNT, false>(sc, sc.root_entry, r, inv, tmin, key, stack, best, cnt);
+        return best;
+    }
+    float closest = RTR_INF;  // closest_so_far (scene.rs:144)
+    for (uint32_t i = 0; i < sc.n_objects; ++i) {
+        const uint32_t entry = sc.objects[i].entry;
+        const uint32_t kind = RTR_REF_KIND(entry);
+        if (kind == REF_SPHERE) {
+            float t;
+            if (COUNT) cnt->spheres++;
+            if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(entry)), r, tmin, closest, t)) {
+                closest = t; best.t = t; best.ref = entry;
+            }
+        } else if (kind == REF_VOLUME) {
+            float t = volume_hit(sc, sc.volumes[RTR_REF_INDEX(entry)], r, inv, tmin, closest, key, stack, EXHAUSTIVE,
+                                 COUNT ? cnt : nullptr);
+            if (t == t) { closest = t; best.t = t; best.ref = entry; }
+        } else if (kind != REF_EMPTY) {
+            // mesh: its own closest hit, tmax ignored, unconditionally replaces the result (Q9)
+            LiteHit m; m.t = RTR_INF; m.ref = REF_EMPTY_VALUE; m.u = m.v = 0.0f;
+            walk<EXHAUSTIVE, COUNT, true>(sc, entry, r, inv, tmin, key, stack, m, cnt);
+            if (m.ref != REF_EMPTY_VALUE) { closest = m.t; best = m; }
+        }
+    }
+    return best;
+}
+
+// ------------------------------------------------------------------ HitRecord for the winner
+struct Hit {
+    v3 point, normal;
+    float t;
+    bool front_face;
+    uint32_t material, object, primitive;
+};
+
+// Rebuilds what the reference's hit() returned for the winning primitive:
+// objects.rs:45-50, mesh.rs:184-192, volume.rs:66-71, then HitRecord::new (ray.rs:39-54)
+__device__ __forceinline__ Hit finish_hit(const SceneView& sc, const Ray& r, const LiteHit& lh) {
+    Hit h;
+    const uint32_t kind = RTR_REF_KIND(lh.ref), i = RTR_REF_INDEX(lh.ref);
+    v3 n;
+    h.t = lh.t;
+    h.point = ray_at(r, lh.t);
+    if (kind == REF_SPHERE) {
+        const float4 s = ldg4(sc.spheres + i);
+        const uint4 info = ldgu4(sc.sphere_info + i);
+        n = (h.point - xyz(s)) / s.w;
+        h.object = info.x; h.primitive = 0; h.material = info.z;
+    } else if (kind == REF_TRI) {
+        const F4* q = sc.tris + (size_t)i * 3;
+        const F4* vn = sc.tri_vn + (size_t)i * 3;
+        const v3 fn = mk(__ldg(&q[0].w), __ldg(&q[1].w), __ldg(&q[2].w));
+        const v3 n0 = xyz(ldg4(vn)), n1 = xyz(ldg4(vn + 1)), n2 = xyz(ldg4(vn + 2));
+        const uint4 info = ldgu4(sc.tri_info + i);
+        n = lh.u * n1 + lh.v * n2 + (1.0f - lh.u - lh.v) * n0;  // mesh.rs:185
+        // `normal.angle(face).0 > 0` (mesh.rs:187) with angle = atan2(|n x f|, n.f):
+        // atan2(y>=0, x) > 0  <=>  y > 0 || (y == 0 && x negative (incl. -0)); NaN -> false
+        const float y = magnitude(cross(n, fn)), x = dot(n, fn);
+        if (y > 0.0f || (y == 0.0f && (__float_as_uint(x) >> 31) && x == x)) n = fn;
+        h.object = info.x; h.primitive = info.y; h.material = info.z;
+    } else {
+        const VolumeRec& vol = sc.volumes[i];
+        n = mk(1.0f, 0.0f, 0.0f);
+        h.object = vol.object; h.primitive = 0; h.material = vol.material;
+    }
+    h.front_face = dot(r.d, n) < 0.0f;
+    h.normal = h.front_face ? n : -n;
+    return h;
+}
+
+// ------------------------------------------------------------------ materials
+__device__ __forceinline__ bool near_zero(v3 v) {  // math.rs:6-9
+    const float EPS = 1.0e-8f;
+    return fabsf(v.x) < EPS && fabsf(v.y) < EPS && fabsf(v.z) < EPS;
+}
+__device__ __forceinline__ v3 reflect(v3 v, v3 n) { return v - 2.0f * dot(v, n) * n; }  // math.rs:12-14
+__device__ __forceinline__ v3 refract(v3 uv, v3 n, float eta) {                         // math.rs:16-21
+    float cos_theta = fminf(dot(n, -uv), 1.0f);
+    v3 out_perp = eta * (uv + cos_theta * n);
+    v3 out_parallel = -sqrtf(fabsf(1.0f - dot(out_perp, out_perp))) * n;
+    return out_perp + out_parallel;
+}
+__device__ __forceinline__ float powi5(float a) { float a2 = a * a; float a4 = a2 * a2; return a * a4; }
+__device__ __forceinline__ float reflectance(float cosine, float idx) {  // materials.rs:103-108
+    float r0 = (1.0f - idx) / (1.0f + idx);
+    r0 = r0 * r0;
+    return r0 + (1.0f - r0) * powi5(1.0f - cosine);
+}
+
+struct Scatter { v3 attenuation; bool some; Ray ray; };
+
+__device__ __forceinline__ Scatter lambertian_scatter(v3 albedo, const Hit& hit, const RngKey& key) {  // :31-41
+    v3 dir = hit.normal + sample_unit_sphere_surface(key);
+    if (near_zero(dir)) dir = hit.normal;
+    Scatter s; s.attenuation = albedo; s.some = true; s.ray.o = hit.point; s.ray.d = dir;
+    return s;
+}
+
+// Material::scatter for Scene.material(handle); MixMaterial unrolled into a loop (materials.rs:150-156)
+__device__ __forceinline__ Scatter scatter(const SceneView& sc, uint32_t material, const Ray& ray, const Hit& hit,
+                                           const RngKey& key) {
+    MaterialRec m = sc.materials[material];
+    for (uint32_t level = 0; m.kind == RTR_MAT_MIX; ++level) {
+        const bool first = gen_range_01(draw(key, P_MIX, level).x) >= m.param;
+        m = sc.materials[first ? m.first : m.second];
+    }
+    Scatter s;
+    s.ray.o = hit.point;
+    s.ray.d = mk(0.0f, 0.0f, 0.0f);
+    const v3 color = mk(m.r, m.g, m.b);
+    switch (m.kind) {
+        case RTR_MAT_LAMBERTIAN: return lambertian_scatter(color, hit, key);
+        case RTR_MAT_METAL: {  // :58-70
+            v3 reflected = normalize(reflect(ray.d, hit.normal));
+            s.ray.d = reflected + m.param * sample_unit_sphere_surface(key);
+            s.some = dot(s.ray.d, hit.normal) > 0.0f;
+            s.attenuation = s.some ? color : mk(0.0f, 0.0f, 0.0f);
+            return s;
+        }
+        case RTR_MAT_EMISSION: s.some = false; s.attenuation = color; return s;  // :88-90
+        case RTR_MAT_DIELECTRIC: {  // :113-138
+            const float ir = m.param;
+            const float ratio = hit.front_face ? 1.0f / ir : ir;
+            const v3 unit = normalize(ray.d);
+            const float cos_theta = fminf(dot(hit.normal, -unit), 1.0f);
+            const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+            const bool cannot_refract = (ratio * sin_theta) > 1.0f;
+            bool refl = cannot_refract;
+            if (!refl) refl = reflectance(cos_theta, ratio) > gen_range_01(draw(key, P_DIELECTRIC, 0).x);
+            s.ray.d = refl ? reflect(unit, hit.normal) : refract(unit, hit.normal, ratio);
+            s.some = true; s.attenuation = mk(1.0f, 1.0f, 1.0f);
+            return s;
+        }
+        default:  // Isotropic (volume.rs:82-87)
+            s.ray.d = sample_unit_sphere_volume(key);
+            s.some = true; s.attenuation = color;
+            return s;
+    }
+}
+
+// ------------------------------------------------------------------ backgrounds (backgrounds.rs)
+// Rust `f32 as usize` saturates (NaN -> 0); __float2ull_rz saturates the same way, NaN -> 0x8000...
+__device__ __forceinline__ unsigned long long f32_as_usize(float v) {
+    return (v == v) ? __float2ull_rz(v) : 0ull;
+}
+__device__ __forceinline__ v3 background_sample(const SceneView& sc, const Ray& ray, Counters* cnt) {
+    const BackgroundRec& bg = sc.background;
+    if (bg.kind == RTR_BG_UNIFORM) return mk(bg.r, bg.g, bg.b);  // :27-29
+    if (bg.kind == RTR_BG_GRADIENT) {                            // :46-48, ray.rs:19-26
+        float t = 0.5f * (normalize(ray.d).y + 1.0f);
+        return mk(bg.r, bg.g, bg.b) * (1.0f - t) + mk(bg.br, bg.bg, bg.bb) * t;
+    }
+    // SkyMap::sample :85-92, to_spherical_coords math.rs:24-29
+    const v3 d = normalize(ray.d);
+    const float sx = acosf(-d.y);
+    const float sy = atan2f(-d.z, d.x) + RTR_PI;
+    const float u = sx / RTR_PI;
+    const float v = sy / (2.0f * RTR_PI);
+    const unsigned long long W = bg.width, H = bg.height;
+    const unsigned long long x = f32_as_usize(v * (float)W) % W;
+    const unsigned long long y = H - 1ull - f32_as_usize(u * (float)H) % H;
+    if (cnt) cnt->env++;
+    const float4 texel = ldg4(sc.env + (x + y * W));
+    return mk(texel.x, texel.y, texel.z);
+}
+
+// ------------------------------------------------------------------ camera (camera.rs:19-24)
+__device__ __forceinline__ Ray camera_sample_ray(const CameraBasis& cam, uint32_t W, uint32_t H, uint32_t x,
+                                                 uint32_t y, const RngKey& key) {
+    const uint4 j = draw(key, P_JITTER, 0);
+    const float u = ((float)x + gen_range_01_inclusive(j.x)) / (float)(W - 1);  // render.rs:88-89
+    const float v = ((float)y + gen_range_01_inclusive(j.y)) / (float)(H - 1);
+    Ray r;
+    r.o = cam.origin;
+    r.d = cam.lower_left_corner + cam.horizontal * u - cam.vertical * v - cam.origin;
+    return r;
+}
+
+// f32::clamp(0, hi): NaN stays NaN (render.rs:95-97)
+__device__ __forceinline__ float f32_clamp(float v, float lo, float hi) {
+    if (v < lo) return lo;
+    if (v > hi) return hi;
+    return v;
+}
+// Rust `f32 as u8`: saturating, NaN -> 0 (color.rs:34-41)
+__device__ __forceinline__ uint8_t f32_as_u8(float v) {
+    if (!(v == v) || v <= 0.0f) return 0;
+    if (v >= 255.0f) return 255;
+    return (uint8_t)__float2uint_rz(v);
+}
+
+}  // namespace rtr

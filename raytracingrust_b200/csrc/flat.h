@@ -1,0 +1,97 @@
+// flat.h — the flattened, device-resident scene layout (host + device view).
+//
+// Produced once per rtr_scene_upload by host_flatten.cpp from the reference's pointer BVH
+// topology (lib/core/bvh.rs:59-144 for the scene and, nested, for every mesh
+// lib/core/mesh.rs:119-121).  The two levels are fused into ONE linear node array: the
+// top-level leaf of a mesh object is simply that mesh's root.
+//
+// Node (64 B, 64-B aligned, 4 x float4) — a Split node stores the boxes its CHILDREN would
+// test on entry (bvh.rs:161), so one fetch yields both slab tests and the near/far order:
+//   q0 = { left.min.xyz , bits(left_ref)  }
+//   q1 = { left.max.xyz , bits(right_ref) }
+//   q2 = { right.min.xyz, 0 }
+//   q3 = { right.max.xyz, 0 }
+// Leaves carry no box (bvh.rs:157-159, quirk Q3): a leaf child is tested unconditionally once
+// its parent's box was pierced.  A tree root has no parent, so every root that is a Split gets
+// a pseudo parent {left = root + its own box, right = EMPTY}; queries start at that "entry".
+//
+// Child reference (u32): kind in bits 31..29, index in bits 28..0.
+#ifndef RTR_FLAT_H_
+#define RTR_FLAT_H_
+
+#include <stdint.h>
+
+namespace rtr {
+
+enum : uint32_t {
+    REF_NODE = 0u,    // index of a 64-B node
+    REF_SPHERE = 1u,  // slot in spheres[] / sphere_info[]
+    REF_TRI = 2u,     // slot in tris[] (x3) / tri_vn[] (x3) / tri_info[]
+    REF_VOLUME = 3u,  // index in volumes[]
+    REF_EMPTY = 7u    // BvhNode::None
+};
+#define RTR_REF_KIND(r) ((r) >> 29)
+#define RTR_REF_INDEX(r) ((r)&0x1FFFFFFFu)
+#define RTR_MAKE_REF(kind, idx) (((uint32_t)(kind) << 29) | (uint32_t)(idx))
+static const uint32_t REF_EMPTY_VALUE = 0xFFFFFFFFu;  // kind 7
+
+struct F4 { float x, y, z, w; };
+struct U4 { uint32_t x, y, z, w; };
+
+// per-primitive side record, fetched once per ray for the winning hit only
+//   x = Scene.objects index, y = triangle index inside its mesh (original order),
+//   z = material index, w = DFS leaf rank (tie-break: among equal t the LAST leaf in the
+//       reference's left-to-right DFS wins, bvh.rs:183-187, quirk Q2)
+typedef U4 PrimInfo;
+
+struct VolumeRec {        // Volume (lib/volume.rs:19-31)
+    uint32_t entry;       // ref of the boundary: SPHERE slot | NODE (pseudo parent) | TRI | EMPTY
+    float neg_inv_density;
+    uint32_t material;    // boundary.material()
+    uint32_t object;      // Scene.objects index
+    uint32_t rank;        // DFS leaf rank of the volume leaf
+    uint32_t index;       // index in rtr_scene_desc.volumes (RNG iteration slot)
+    uint32_t _pad[2];
+};
+
+struct ObjectRec {        // Scene.objects[i], for the BVH-off linear scan (scene.rs:141-156)
+    uint32_t entry;       // SPHERE slot | NODE (pseudo parent) | TRI | VOLUME | EMPTY
+    uint32_t _pad[3];
+};
+
+struct MaterialRec {      // Box<dyn Material>
+    uint32_t kind;
+    float r, g, b;
+    float param;
+    uint32_t first, second;
+    uint32_t _pad;
+};
+
+struct BackgroundRec {
+    uint32_t kind;
+    float r, g, b;        // uniform | gradient top
+    float br, bg, bb;     // gradient bottom
+    uint32_t width, height;
+};
+
+// Device view: raw pointers into one allocation each.
+struct SceneView {
+    const F4* nodes;          // 4 per node
+    const F4* spheres;        // (cx, cy, cz, r) per slot
+    const PrimInfo* sphere_info;
+    const F4* tris;           // 3 per slot: (v0.xyz, fn.x) (e1.xyz, fn.y) (e2.xyz, fn.z)
+    const F4* tri_vn;         // 3 per slot: vertex normals n0, n1, n2 (w unused)
+    const PrimInfo* tri_info;
+    const VolumeRec* volumes;
+    const ObjectRec* objects;
+    const MaterialRec* materials;
+    const F4* env;            // SkyMap texels as float4 (rgb, 0)
+    BackgroundRec background;
+    uint32_t root_entry;      // entry ref of the scene tree
+    uint32_t n_objects;
+    uint32_t n_materials;
+    uint32_t n_volumes;
+};
+
+}  // namespace rtr
+#endif

@@ -1,0 +1,325 @@
+// host_flatten.cpp — rebuild the reference BVH topology and flatten it (flat.h).
+//
+// Host-side mirror of:
+//   BvhNode::from_list           lib/core/bvh.rs:59-144   (median split, stable sort, n/2)
+//   AABB surround/centroid/...   lib/utils/aabb.rs:21-78
+//   Sphere::bounds               lib/objects.rs:53-60
+//   Mesh::from_buffers / bounds  lib/core/mesh.rs:78-117,200-213
+//   Volume::bounds / ::new       lib/volume.rs:26-31,89-93
+// The topology decides exact-t ties (leaf DFS rank), so it is reproduced, not improved.
+// Compiled with -ffp-contract=off: every box coordinate must equal the reference's f32 value.
+#include "host_flatten.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace rtr {
+
+namespace {
+
+struct V3 { float x, y, z; };
+struct Box { V3 min, max; };
+
+inline V3 v3(const float* p) { return V3{p[0], p[1], p[2]}; }
+inline V3 sub(V3 a, V3 b) { return V3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V3 cross(V3 a, V3 b) { return V3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline float dot(V3 a, V3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline V3 normalize(V3 a) { float s = 1.0f / std::sqrt(dot(a, a)); return V3{a.x * s, a.y * s, a.z * s}; }
+
+inline Box surround(const Box& a, const Box& b) {  // aabb.rs:41-54 (f32::min/max ignore a NaN operand)
+    return Box{V3{std::fmin(a.min.x, b.min.x), std::fmin(a.min.y, b.min.y), std::fmin(a.min.z, b.min.z)},
+               V3{std::fmax(a.max.x, b.max.x), std::fmax(a.max.y, b.max.y), std::fmax(a.max.z, b.max.z)}};
+}
+inline V3 centroid(const Box& b) {  // aabb.rs:28-30
+    return V3{(b.min.x + b.max.x) / 2.0f, (b.min.y + b.max.y) / 2.0f, (b.min.z + b.max.z) / 2.0f};
+}
+inline Box epsilon_expand(Box b, float eps) {  // aabb.rs:57-78
+    V3 c = centroid(b);
+    Box r = b;
+    if (b.max.x - b.min.x < eps) { r.min.x = c.x - eps; r.max.x = c.x + eps; }
+    if (b.max.y - b.min.y < eps) { r.min.y = c.y - eps; r.max.y = c.y + eps; }
+    if (b.max.z - b.min.z < eps) { r.min.z = c.z - eps; r.max.z = c.z + eps; }
+    return r;
+}
+
+struct Built {
+    uint32_t ref;   // child reference as stored in the parent
+    Box box;        // own box (valid iff split)
+    bool split;
+    uint32_t depth; // levels below and including this node
+};
+
+// Anything BvhNode::from_list can be built over (bvh.rs:18-28)
+struct Collection {
+    virtual ~Collection() {}
+    virtual Box bounds(uint32_t handle) const = 0;
+    virtual Built leaf(uint32_t handle) = 0;  // emit the leaf, return its child reference
+};
+
+struct Flattener {
+    HostFlat& out;
+    const rtr_scene_desc& d;
+    std::string& err;
+    uint32_t rank = 0;
+
+    Flattener(HostFlat& o, const rtr_scene_desc& desc, std::string& e) : out(o), d(desc), err(e) {}
+
+    uint32_t alloc_node() {
+        uint32_t idx = (uint32_t)(out.nodes.size() / 4);
+        out.nodes.resize(out.nodes.size() + 4, F4{0, 0, 0, 0});
+        return idx;
+    }
+    static float bits(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+    void write_node(uint32_t idx, const Built& l, const Built& r) {
+        F4* q = &out.nodes[(size_t)idx * 4];
+        Box lb = l.split ? l.box : Box{{0, 0, 0}, {0, 0, 0}};
+        Box rb = r.split ? r.box : Box{{0, 0, 0}, {0, 0, 0}};
+        q[0] = F4{lb.min.x, lb.min.y, lb.min.z, bits(l.ref)};
+        q[1] = F4{lb.max.x, lb.max.y, lb.max.z, bits(r.ref)};
+        q[2] = F4{rb.min.x, rb.min.y, rb.min.z, 0.0f};
+        q[3] = F4{rb.max.x, rb.max.y, rb.max.z, 0.0f};
+    }
+
+    // BvhNode::from_list (bvh.rs:59-144).  `handles` is consumed.
+    Built build(std::vector<uint32_t>& handles, Collection& coll) {
+        const size_t n = handles.size();
+        if (n == 0) return Built{REF_EMPTY_VALUE, Box{}, false, 0};  // BvhNode::None
+        if (n == 1) return coll.leaf(handles[0]);                    // BvhNode::Object
+        std::vector<Box> b(n);
+        for (size_t i = 0; i < n; ++i) b[i] = coll.bounds(handles[i]);
+        Box bounds = b[0];                                           // :68-72
+        for (size_t i = 1; i < n; ++i) bounds = surround(bounds, b[i]);
+        V3 c0 = centroid(b[0]);                                      // :75-79
+        Box cents{c0, c0};
+        for (size_t i = 1; i < n; ++i) { V3 c = centroid(b[i]); cents = surround(cents, Box{c, c}); }
+        V3 spread = sub(cents.max, cents.min);
+        int axis = (spread.x > spread.y && spread.x > spread.z) ? 0
+                 : (spread.y > spread.x && spread.y > spread.z) ? 1 : 2;  // :81-88
+        std::vector<float> key(n);
+        for (size_t i = 0; i < n; ++i) {
+            V3 c = centroid(b[i]);
+            key[i] = axis == 0 ? c.x : axis == 1 ? c.y : c.z;
+            if (!(key[i] == key[i])) { err = "NaN centroid (the reference panics at bvh.rs:99)"; return Built{REF_EMPTY_VALUE, Box{}, false, 0}; }
+        }
+        std::vector<uint32_t> order(n);
+        for (size_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+        // Rust's slice::sort_by is a stable merge sort; with a strict weak order the result is unique
+        std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return key[x] < key[y]; });
+        std::vector<uint32_t> left, right;                            // :125-134
+        left.reserve(n / 2); right.reserve(n - n / 2);
+        for (size_t i = 0; i < n; ++i) (i < n / 2 ? left : right).push_back(handles[order[i]]);
+        handles.clear(); handles.shrink_to_fit();
+        b.clear(); b.shrink_to_fit(); key.clear(); key.shrink_to_fit(); order.clear(); order.shrink_to_fit();
+        uint32_t idx = alloc_node();  // pre-order index: a subtree is contiguous in memory
+        Built l = build(left, coll);
+        if (!err.empty()) return l;
+        Built r = build(right, coll);
+        if (!err.empty()) return r;
+        write_node(idx, l, r);
+        return Built{RTR_MAKE_REF(REF_NODE, idx), bounds, true, 1 + std::max(l.depth, r.depth)};
+    }
+
+    // wrap a root so its own box is tested on entry (see flat.h)
+    uint32_t make_entry(const Built& root, uint32_t* depth) {
+        *depth = root.depth;
+        if (!root.split) return root.ref;
+        uint32_t idx = alloc_node();
+        write_node(idx, root, Built{REF_EMPTY_VALUE, Box{}, false, 0});
+        *depth = root.depth + 1;
+        return RTR_MAKE_REF(REF_NODE, idx);
+    }
+
+    // ---- leaves -------------------------------------------------------------
+    Built emit_sphere(uint32_t sphere_index, uint32_t object) {
+        const rtr_sphere& s = d.spheres[sphere_index];
+        uint32_t slot = (uint32_t)out.spheres.size();
+        out.spheres.push_back(F4{s.center.x, s.center.y, s.center.z, s.radius});
+        out.sphere_info.push_back(PrimInfo{object, 0u, s.material, rank++});
+        return Built{RTR_MAKE_REF(REF_SPHERE, slot), Box{}, false, 1};
+    }
+
+    struct MeshColl : Collection {
+        Flattener& f;
+        const rtr_mesh& m;
+        uint32_t object;
+        MeshColl(Flattener& fl, const rtr_mesh& mesh, uint32_t obj) : f(fl), m(mesh), object(obj) {}
+        Box bounds(uint32_t h) const override {  // mesh.rs:201-213
+            const uint32_t* t = &m.indices[3 * (size_t)h];
+            V3 a = v3(&m.positions[3 * (size_t)t[0]]), b = v3(&m.positions[3 * (size_t)t[1]]), c = v3(&m.positions[3 * (size_t)t[2]]);
+            return epsilon_expand(surround(Box{a, a}, surround(Box{b, b}, Box{c, c})), 0.01f);
+        }
+        Built leaf(uint32_t h) override {
+            const uint32_t* t = &m.indices[3 * (size_t)h];
+            V3 p0 = v3(&m.positions[3 * (size_t)t[0]]), p1 = v3(&m.positions[3 * (size_t)t[1]]), p2 = v3(&m.positions[3 * (size_t)t[2]]);
+            // face normal as Mesh::from_buffers computes it (mesh.rs:85-90)
+            V3 fn = normalize(cross(sub(p2, p1), sub(p0, p1)));
+            // edges as Triangle::hit computes them (mesh.rs:160-161)
+            V3 e1 = sub(p1, p0), e2 = sub(p2, p0);
+            uint32_t slot = (uint32_t)f.out.tri_info.size();
+            f.out.tris.push_back(F4{p0.x, p0.y, p0.z, fn.x});
+            f.out.tris.push_back(F4{e1.x, e1.y, e1.z, fn.y});
+            f.out.tris.push_back(F4{e2.x, e2.y, e2.z, fn.z});
+            for (int k = 0; k < 3; ++k) {
+                const float* nn = &m.normals[3 * (size_t)t[k]];
+                f.out.tri_vn.push_back(F4{nn[0], nn[1], nn[2], 0.0f});
+            }
+            f.out.tri_info.push_back(PrimInfo{object, h, m.material, f.rank++});
+            return Built{RTR_MAKE_REF(REF_TRI, slot), Box{}, false, 1};
+        }
+    };
+
+    Built emit_mesh(uint32_t mesh_index, uint32_t object) {
+        const rtr_mesh& m = d.meshes[mesh_index];
+        MeshColl coll(*this, m, object);
+        std::vector<uint32_t> handles(m.n_indices / 3);
+        for (size_t i = 0; i < handles.size(); ++i) handles[i] = (uint32_t)i;
+        return build(handles, coll);  // mesh.build_bvh() (mesh.rs:119-121)
+    }
+
+    Box object_bounds(rtr_object_ref ref) const {
+        if (ref.kind == RTR_OBJ_SPHERE) {  // objects.rs:53-60
+            const rtr_sphere& s = d.spheres[ref.index];
+            return Box{V3{s.center.x - s.radius, s.center.y - s.radius, s.center.z - s.radius},
+                       V3{s.center.x + s.radius, s.center.y + s.radius, s.center.z + s.radius}};
+        }
+        if (ref.kind == RTR_OBJ_MESH) {  // mesh.rs:99-108: seeded with AABB::default() = origin
+            const rtr_mesh& m = d.meshes[ref.index];
+            Box b{{0, 0, 0}, {0, 0, 0}};
+            for (uint32_t i = 0; i < m.n_vertices; ++i) { V3 p = v3(&m.positions[3 * (size_t)i]); b = surround(b, Box{p, p}); }
+            return b;
+        }
+        return object_bounds(d.volumes[ref.index].boundary);  // volume.rs:89-93
+    }
+
+    struct SceneColl : Collection {
+        Flattener& f;
+        std::vector<Box> cached;
+        std::vector<Built> built;  // per object: its leaf as emitted (for the linear-scan table)
+        explicit SceneColl(Flattener& fl) : f(fl) {
+            cached.resize(f.d.n_objects);
+            built.resize(f.d.n_objects, Built{REF_EMPTY_VALUE, Box{}, false, 0});
+            for (uint32_t i = 0; i < f.d.n_objects; ++i) cached[i] = f.object_bounds(f.d.objects[i]);
+        }
+        Box bounds(uint32_t h) const override { return cached[h]; }
+        Built leaf(uint32_t h) override { return built[h] = f.emit_object(f.d.objects[h], h); }
+    };
+
+    Built emit_object(rtr_object_ref ref, uint32_t object) {
+        if (ref.kind == RTR_OBJ_SPHERE) return emit_sphere(ref.index, object);
+        if (ref.kind == RTR_OBJ_MESH) return emit_mesh(ref.index, object);
+        // Volume: the leaf is the volume; its boundary is a separate tree queried twice per visit
+        const rtr_volume& v = d.volumes[ref.index];
+        VolumeRec rec;
+        std::memset(&rec, 0, sizeof(rec));
+        rec.rank = rank++;
+        uint32_t bdepth = 0;
+        Built b = emit_object(v.boundary, object);
+        rec.entry = make_entry(b, &bdepth);
+        out.max_boundary_depth = std::max(out.max_boundary_depth, bdepth);
+        rec.neg_inv_density = v.neg_inv_density;  // as stored by Volume::new (volume.rs:26-31)
+        rec.material = v.boundary.kind == RTR_OBJ_SPHERE ? d.spheres[v.boundary.index].material
+                                                         : d.meshes[v.boundary.index].material;
+        rec.object = object;
+        rec.index = ref.index;
+        uint32_t vi = (uint32_t)out.volumes.size();
+        out.volumes.push_back(rec);
+        return Built{RTR_MAKE_REF(REF_VOLUME, vi), Box{}, false, 1};
+    }
+};
+
+bool validate(const rtr_scene_desc& d, std::string& err) {
+    auto bad = [&](const char* m) { err = m; return false; };
+    if ((d.n_objects && !d.objects) || (d.n_spheres && !d.spheres) || (d.n_meshes && !d.meshes) ||
+        (d.n_volumes && !d.volumes) || (d.n_materials && !d.materials))
+        return bad("null array with non-zero count");
+    auto ref_ok = [&](rtr_object_ref r, bool allow_volume) {
+        if (r.kind == RTR_OBJ_SPHERE) return r.index < d.n_spheres;
+        if (r.kind == RTR_OBJ_MESH) return r.index < d.n_meshes;
+        if (r.kind == RTR_OBJ_VOLUME) return allow_volume && r.index < d.n_volumes;
+        return false;
+    };
+    for (uint32_t i = 0; i < d.n_objects; ++i)
+        if (!ref_ok(d.objects[i], true)) return bad("object reference out of range");
+    for (uint32_t i = 0; i < d.n_volumes; ++i) {
+        if (d.volumes[i].boundary.kind == RTR_OBJ_VOLUME) { err = "Volume bounded by a Volume is unsupported"; return false; }
+        if (!ref_ok(d.volumes[i].boundary, false)) return bad("volume boundary out of range");
+    }
+    for (uint32_t i = 0; i < d.n_spheres; ++i)
+        if (d.spheres[i].material >= d.n_materials) return bad("sphere material handle out of range");
+    for (uint32_t i = 0; i < d.n_meshes; ++i) {
+        const rtr_mesh& m = d.meshes[i];
+        if (m.material >= d.n_materials) return bad("mesh material handle out of range");
+        if ((m.n_vertices && (!m.positions || !m.normals)) || (m.n_indices && !m.indices)) return bad("mesh with null buffers");
+        for (uint32_t k = 0; k < m.n_indices; ++k)
+            if (m.indices[k] >= m.n_vertices) return bad("mesh vertex index out of range");
+    }
+    for (uint32_t i = 0; i < d.n_materials; ++i) {
+        const rtr_material& m = d.materials[i];
+        if (m.kind > RTR_MAT_ISOTROPIC) return bad("unknown material kind");
+        if (m.kind == RTR_MAT_MIX && (m.first >= d.n_materials || m.second >= d.n_materials)) return bad("MixMaterial child out of range");
+    }
+    // a MixMaterial cycle would recurse forever in the reference; reject
+    for (uint32_t i = 0; i < d.n_materials; ++i) {
+        if (d.materials[i].kind != RTR_MAT_MIX) continue;
+        std::vector<uint32_t> stack{i};
+        uint32_t steps = 0;
+        while (!stack.empty()) {
+            uint32_t k = stack.back(); stack.pop_back();
+            if (++steps > 4 * d.n_materials + 8) return bad("MixMaterial cycle or nesting too deep");
+            if (d.materials[k].kind == RTR_MAT_MIX) { stack.push_back(d.materials[k].first); stack.push_back(d.materials[k].second); }
+        }
+    }
+    if (d.background.kind > RTR_BG_SKYMAP) return bad("unknown background kind");
+    if (d.background.kind == RTR_BG_SKYMAP && (!d.background.texels || !d.background.width || !d.background.height))
+        return bad("SkyMap without texels");
+    return true;
+}
+
+}  // namespace
+
+int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err) {
+    if (!validate(d, err)) return err.find("unsupported") != std::string::npos ? RTR_UNSUPPORTED : RTR_INVALID_ARG;
+    Flattener f(out, d, err);
+    out.nodes.reserve(64);
+    Flattener::SceneColl coll(f);
+    std::vector<uint32_t> handles(d.n_objects);
+    for (uint32_t i = 0; i < d.n_objects; ++i) handles[i] = i;
+    Built root = f.build(handles, coll);  // scene.build_bvh() (scene.rs:112-114)
+    if (!err.empty()) return RTR_INVALID_ARG;
+    uint32_t depth = 0;
+    out.root_entry = f.make_entry(root, &depth);
+    out.max_depth = depth;
+
+    // linear-scan table (scene.rs:141-156): one entry per object, in add_object order.  A mesh
+    // root that is a Split needs its own box tested on entry -> pseudo parent per mesh object.
+    out.objects.resize(d.n_objects);
+    for (uint32_t i = 0; i < d.n_objects; ++i) {
+        std::memset(&out.objects[i], 0, sizeof(ObjectRec));
+        uint32_t dd = 0;
+        out.objects[i].entry = f.make_entry(coll.built[i], &dd);
+    }
+    out.materials.resize(d.n_materials);
+    for (uint32_t i = 0; i < d.n_materials; ++i) {
+        const rtr_material& m = d.materials[i];
+        MaterialRec r;
+        std::memset(&r, 0, sizeof(r));
+        r.kind = m.kind; r.r = m.color.x; r.g = m.color.y; r.b = m.color.z;
+        r.param = m.param; r.first = m.first; r.second = m.second;
+        out.materials[i] = r;
+    }
+    std::memset(&out.background, 0, sizeof(out.background));
+    out.background.kind = d.background.kind;
+    out.background.r = d.background.color.x; out.background.g = d.background.color.y; out.background.b = d.background.color.z;
+    out.background.br = d.background.bottom.x; out.background.bg = d.background.bottom.y; out.background.bb = d.background.bottom.z;
+    if (d.background.kind == RTR_BG_SKYMAP) {
+        out.background.width = d.background.width; out.background.height = d.background.height;
+        size_t n = (size_t)d.background.width * d.background.height;
+        out.env.resize(n);
+        for (size_t k = 0; k < n; ++k)
+            out.env[k] = F4{d.background.texels[3 * k], d.background.texels[3 * k + 1], d.background.texels[3 * k + 2], 0.0f};
+    }
+    return RTR_OK;
+}
+
+}  // namespace rtr

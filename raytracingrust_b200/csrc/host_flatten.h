@@ -1,0 +1,29 @@
+// host_flatten.h — host image of the flattened scene (see flat.h, host_flatten.cpp)
+#ifndef RTR_HOST_FLATTEN_H_
+#define RTR_HOST_FLATTEN_H_
+
+#include <string>
+#include <vector>
+
+#include "../../include/rtr.h"
+#include "flat.h"
+
+namespace rtr {
+
+struct HostFlat {
+    std::vector<F4> nodes, spheres, tris, tri_vn, env;
+    std::vector<PrimInfo> sphere_info, tri_info;
+    std::vector<VolumeRec> volumes;
+    std::vector<ObjectRec> objects;
+    std::vector<MaterialRec> materials;
+    BackgroundRec background;
+    uint32_t root_entry = 0xFFFFFFFFu;
+    uint32_t max_depth = 0;           // levels of the fused scene tree incl. the pseudo parent
+    uint32_t max_boundary_depth = 0;  // deepest volume-boundary tree
+};
+
+// returns an rtr_status; on failure `err` says why
+int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err);
+
+}  // namespace rtr
+#endif

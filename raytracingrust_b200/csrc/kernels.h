@@ -1,0 +1,56 @@
+// kernels.h — host-visible launch interface of kernels.cu (plain structs, no device code)
+#ifndef RTR_KERNELS_H_
+#define RTR_KERNELS_H_
+
+#include <cuda_runtime_api.h>
+#include <vector_types.h>
+#include <stdint.h>
+
+#include "../../include/rtr.h"
+#include "flat.h"
+
+namespace rtr {
+
+#define RTR_MEGA_THREADS 128
+
+struct v3 { float x, y, z; };
+
+// RayOrigin (lib/core/camera.rs:11-16), computed once per render on the host
+struct CameraBasis { v3 origin, horizontal, vertical, lower_left_corner; };
+
+enum { STAT_RAYS = 0, STAT_NODES = 1, STAT_TRIS = 2, STAT_SPHERES = 3, STAT_ENV = 4, STAT_COUNT = 8 };
+
+struct RenderArgs {
+    SceneView sc;
+    CameraBasis cam;
+    uint32_t width, height;
+    uint32_t max_ray_depth;
+    float clamp_indirect;
+    uint32_t enable_bvh_tree;
+    uint32_t mode;
+    uint32_t k0, k1;             // Philox key = seed
+    uint32_t sample_begin, sample_count;
+    uint32_t tiles_x, n_tiles;   // 8x4-pixel warp tiles
+    uint32_t n_chunks, chunk_samples;  // sample chunks per tile (1 unless the image is small)
+    float4* accum;               // W*H: (sum r, sum g, sum b, samples)
+    float4* partials;            // n_chunks * W*H when n_chunks > 1
+    uint32_t* work_counter;      // zeroed before launch
+    unsigned long long* stats;   // STAT_COUNT counters
+};
+
+int megakernel_max_blocks_per_sm(bool exhaustive, bool count);
+cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
+cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, cudaStream_t st);
+cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels, float spp, cudaStream_t st);
+cudaError_t launch_trace_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float tmin, uint32_t bvh,
+                               bool exhaustive, uint32_t k0, uint32_t k1, rtr_hit* out, unsigned long long* stats,
+                               cudaStream_t st);
+cudaError_t launch_scatter_batch(const SceneView& sc, const rtr_scatter_in* in, size_t n, uint32_t mode, uint32_t k0,
+                                 uint32_t k1, rtr_scatter_out* out, cudaStream_t st);
+cudaError_t launch_background_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float* rgb, cudaStream_t st);
+cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, uint32_t k0, uint32_t k1,
+                               const uint32_t* pixels, const uint32_t* samples, size_t n, rtr_ray* out,
+                               cudaStream_t st);
+
+}  // namespace rtr
+#endif

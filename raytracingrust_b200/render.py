@@ -1,0 +1,253 @@
+"""ctypes binding of librtr_b200.so + the reference-facing `render(target, scene)` call.
+
+`render` mirrors `pub fn render(target: &mut RenderTarget, scene: &Scene)` (lib/core/render.rs:61):
+it lowers the scene (the reference rebuilds its BVH on every call, render.rs:67), renders on the
+GPU and fills `target.data` with RGBA8.  There is NO CPU fallback: if the CUDA library is missing
+or no device is usable this raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _abi as A
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtr_b200.so")
+_LIB = None
+
+
+class RtrError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"{A.STATUS_NAMES[status] if 0 <= status < len(A.STATUS_NAMES) else status}: {message}")
+        self.status = status
+
+
+def lib():
+    """Load the CUDA library (built in-tree by `make -C raytracingrust_b200/csrc` / __graft_entry__.build)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `make -C {_HERE}/csrc` "
+                          "(there is no CPU fallback for the render path)")
+    L = C.CDLL(LIB_PATH)
+    vp, u32, u64, sz = C.c_void_p, C.c_uint32, C.c_uint64, C.c_size_t
+    L.rtr_abi_version.restype = u32
+    L.rtr_last_error.restype = C.c_char_p
+    L.rtr_last_error.argtypes = [vp]
+    L.rtr_context_create.argtypes = [C.c_int, vp, C.POINTER(vp)]
+    L.rtr_context_destroy.argtypes = [vp]
+    L.rtr_context_destroy.restype = None
+    L.rtr_scene_upload.argtypes = [vp, C.POINTER(A.SceneDesc), C.POINTER(vp)]
+    L.rtr_scene_destroy.argtypes = [vp]
+    L.rtr_scene_destroy.restype = None
+    L.rtr_scene_info.argtypes = [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(C.c_double), C.POINTER(u32), C.POINTER(u32)]
+    L.rtr_render.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp, C.POINTER(A.Stats)]
+    L.rtr_render_accumulate_device.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, C.POINTER(A.Stats)]
+    L.rtr_resolve_device.argtypes = [vp, vp, u32, u32, u32, vp]
+    L.rtr_synchronize.argtypes = [vp]
+    L.rtr_trace_batch.argtypes = [vp, vp, vp, sz, C.c_float, u32, u32, u64, vp, C.POINTER(A.Stats)]
+    L.rtr_scatter_batch.argtypes = [vp, vp, vp, sz, u32, u64, vp]
+    L.rtr_background_batch.argtypes = [vp, vp, vp, sz, vp]
+    L.rtr_camera_rays.argtypes = [vp, C.POINTER(A.RenderParams), vp, vp, sz, vp]
+    L.rtr_scene_load_json.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.rtr_host_scene_desc.argtypes = [vp]
+    L.rtr_host_scene_desc.restype = C.POINTER(A.SceneDesc)
+    L.rtr_host_scene_camera.argtypes = [vp]
+    L.rtr_host_scene_camera.restype = C.POINTER(A.CameraS)
+    L.rtr_host_scene_settings.argtypes = [vp]
+    L.rtr_host_scene_settings.restype = C.POINTER(A.SettingsS)
+    L.rtr_host_scene_destroy.argtypes = [vp]
+    L.rtr_host_scene_destroy.restype = None
+    L.rtr_mesh_load_obj.argtypes = [C.c_char_p, u32, C.POINTER(vp)]
+    L.rtr_host_mesh_get.argtypes = [vp]
+    L.rtr_host_mesh_get.restype = C.POINTER(A.MeshS)
+    L.rtr_host_mesh_destroy.argtypes = [vp]
+    L.rtr_host_mesh_destroy.restype = None
+    if L.rtr_abi_version() != A.RTR_ABI_VERSION:
+        raise ImportError("librtr_b200.so ABI version mismatch")
+    _LIB = L
+    return L
+
+
+def _check(rc, ctx=None):
+    if rc != A.RTR_OK:
+        msg = lib().rtr_last_error(ctx)
+        raise RtrError(rc, msg.decode() if msg else "")
+
+
+def make_params(scene, width, height, seed=0, sample_begin=0, sample_count=0, kernel=A.KERNEL_AUTO, flags=0,
+                settings=None, camera=None):
+    p = A.RenderParams()
+    p.width, p.height = width, height
+    p.camera = (camera or scene.camera).to_c()
+    p.settings = (settings or scene.settings).to_c()
+    p.seed, p.sample_begin, p.sample_count, p.kernel, p.flags = seed, sample_begin, sample_count, kernel, flags
+    return p
+
+
+# ---------------------------------------------------------------------- host loaders
+def load_obj(path):
+    """Mesh::from_file's loader (mesh.rs:63-76): returns (positions Nx3, normals Nx3, indices)."""
+    h = C.c_void_p()
+    _check(lib().rtr_mesh_load_obj(os.fsencode(path), 0, C.byref(h)))
+    try:
+        m = lib().rtr_host_mesh_get(h).contents
+        nv, ni = m.n_vertices, m.n_indices
+        pos = np.ctypeslib.as_array(m.positions, (nv, 3)).copy() if nv else np.zeros((0, 3), np.float32)
+        nrm = np.ctypeslib.as_array(m.normals, (nv, 3)).copy() if nv else np.zeros((0, 3), np.float32)
+        idx = np.ctypeslib.as_array(m.indices, (ni,)).copy() if ni else np.zeros(0, np.uint32)
+    finally:
+        lib().rtr_host_mesh_destroy(h)
+    return pos, nrm, idx
+
+
+class _LoadedScene:
+    """A Scene whose description lives in the library's JSON loader (Scene::from_file)."""
+
+    def __init__(self, path):
+        from .scene import Camera, RenderSettings
+        self._h = C.c_void_p()
+        _check(lib().rtr_scene_load_json(os.fsencode(path), C.byref(self._h)))
+        self.camera = Camera.from_c(lib().rtr_host_scene_camera(self._h).contents)
+        self.settings = RenderSettings.from_c(lib().rtr_host_scene_settings(self._h).contents)
+
+    def lower(self):
+        from .scene import LoweredScene
+        out = LoweredScene()
+        out.desc = lib().rtr_host_scene_desc(self._h).contents
+        out._keep.append(self)
+        return out
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().rtr_host_scene_destroy(self._h)
+            self._h = None
+
+
+def load_scene_json(path):
+    return _LoadedScene(path)
+
+
+# ---------------------------------------------------------------------- device objects
+class Context:
+    """One per GPU / process rank (rtr_context)."""
+
+    def __init__(self, device=0, stream=None):
+        self._h = C.c_void_p()
+        _check(lib().rtr_context_create(device, stream, C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().rtr_context_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def upload(self, scene):
+        return DeviceScene(self, scene)
+
+    def synchronize(self):
+        _check(lib().rtr_synchronize(self._h), self._h)
+
+    def camera_rays(self, params, pixels, samples):
+        pixels = np.ascontiguousarray(pixels, np.uint32)
+        samples = np.ascontiguousarray(samples, np.uint32)
+        rays = np.zeros(len(pixels), A.RAY_DTYPE)
+        _check(lib().rtr_camera_rays(self._h, C.byref(params), pixels.ctypes.data, samples.ctypes.data, len(pixels),
+                                     rays.ctypes.data), self._h)
+        return rays
+
+    def resolve_device(self, accum_ptr, width, height, spp, rgba_ptr):
+        _check(lib().rtr_resolve_device(self._h, accum_ptr, width, height, spp, rgba_ptr), self._h)
+
+
+class DeviceScene:
+    """Flattened scene resident in HBM (rtr_scene)."""
+
+    def __init__(self, ctx, scene):
+        self.ctx = ctx
+        lowered = scene.lower() if hasattr(scene, "lower") else scene
+        self._h = C.c_void_p()
+        _check(lib().rtr_scene_upload(ctx._h, C.byref(lowered.desc), C.byref(self._h)), ctx._h)
+
+    def close(self):
+        if getattr(self, "_h", None) and getattr(self.ctx, "_h", None):
+            lib().rtr_scene_destroy(self._h)
+        self._h = None
+
+    __del__ = close
+
+    def info(self):
+        db, hb, ms, nn, md = C.c_uint64(), C.c_uint64(), C.c_double(), C.c_uint32(), C.c_uint32()
+        _check(lib().rtr_scene_info(self._h, C.byref(db), C.byref(hb), C.byref(ms), C.byref(nn), C.byref(md)))
+        return dict(device_bytes=db.value, h2d_bytes=hb.value, build_ms=ms.value, n_nodes=nn.value, max_depth=md.value)
+
+    def render(self, params, want_rgba=True, want_accum=False):
+        W, H = params.width, params.height
+        rgba = np.zeros((H, W, 4), np.uint8) if want_rgba else None
+        acc = np.zeros((H, W, 4), np.float32) if want_accum else None
+        st = A.Stats()
+        _check(lib().rtr_render(self.ctx._h, self._h, C.byref(params), rgba.ctypes.data if want_rgba else None,
+                                acc.ctypes.data if want_accum else None, C.byref(st)), self.ctx._h)
+        return rgba, acc, st.as_dict()
+
+    def render_into(self, params, rgba_out, accum_out=None):
+        """Same, into caller-owned host buffers (e.g. pinned torch tensors' data_ptr)."""
+        st = A.Stats()
+        _check(lib().rtr_render(self.ctx._h, self._h, C.byref(params), rgba_out, accum_out, C.byref(st)), self.ctx._h)
+        return st.as_dict()
+
+    def render_accumulate_device(self, params, accum_ptr, want_stats=True):
+        st = A.Stats()
+        _check(lib().rtr_render_accumulate_device(self.ctx._h, self._h, C.byref(params), accum_ptr,
+                                                  C.byref(st) if want_stats else None), self.ctx._h)
+        return st.as_dict() if want_stats else None
+
+    def trace_batch(self, rays, tmin=1e-5, enable_bvh_tree=True, flags=0, seed=0, want_stats=False):
+        rays = np.ascontiguousarray(rays, A.RAY_DTYPE)
+        hits = np.zeros(len(rays), A.HIT_DTYPE)
+        st = A.Stats()
+        _check(lib().rtr_trace_batch(self.ctx._h, self._h, rays.ctypes.data, len(rays), tmin, int(enable_bvh_tree),
+                                     flags, seed, hits.ctypes.data, C.byref(st)), self.ctx._h)
+        return (hits, st.as_dict()) if want_stats else hits
+
+    def scatter_batch(self, inp, mode=A.MODE_FULL, seed=0):
+        inp = np.ascontiguousarray(inp, A.SCATTER_IN_DTYPE)
+        out = np.zeros(len(inp), A.SCATTER_OUT_DTYPE)
+        _check(lib().rtr_scatter_batch(self.ctx._h, self._h, inp.ctypes.data, len(inp), mode, seed, out.ctypes.data),
+               self.ctx._h)
+        return out
+
+    def background_batch(self, rays):
+        rays = np.ascontiguousarray(rays, A.RAY_DTYPE)
+        out = np.zeros((len(rays), 3), np.float32)
+        _check(lib().rtr_background_batch(self.ctx._h, self._h, rays.ctypes.data, len(rays), out.ctypes.data), self.ctx._h)
+        return out
+
+
+_DEFAULT_CTX = {}
+
+
+def default_context(device=0):
+    if device not in _DEFAULT_CTX:
+        _DEFAULT_CTX[device] = Context(device)
+    return _DEFAULT_CTX[device]
+
+
+def render(target, scene, seed=0, device=0, kernel=A.KERNEL_AUTO, want_accum=False):
+    """render(&mut target, &scene) (lib/core/render.rs:61-127) on the GPU."""
+    target.request_redraw = True  # render.rs:62
+    ctx = default_context(device)
+    dev_scene = ctx.upload(scene)  # the reference rebuilds the BVH on every call (render.rs:67)
+    try:
+        params = make_params(scene, target.width, target.height, seed=seed, kernel=kernel)
+        rgba, acc, stats = dev_scene.render(params, want_rgba=True, want_accum=want_accum)
+    finally:
+        dev_scene.close()
+    target.data[:] = rgba.reshape(-1)
+    target.accum = acc
+    target.stats = stats
+    return stats
