@@ -148,7 +148,7 @@ typedef struct rtr_stats {
     double upload_ms;        /* host flatten + H2D, filled by rtr_scene_upload queries */
     uint64_t rays;           /* world.hit queries (render.rs:38) */
     uint64_t samples;        /* iterations of render.rs:86 */
-    uint64_t nodes_visited;  /* interior nodes fetched (both child boxes tested) */
+    uint64_t nodes_visited;  /* interior-node boxes slab-tested (32 B each) */
     uint64_t tri_tests;
     uint64_t sphere_tests;
     uint64_t env_lookups;    /* SkyMap texel fetches */

@@ -195,12 +195,11 @@ __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const 
         if (kind == REF_NODE) {
             const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
             const float4 q0 = ldg4(q), q1 = ldg4(q + 1), q2 = ldg4(q + 2), q3 = ldg4(q + 3);
-            if (COUNT) cnt->nodes++;
             uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
             float le = -RTR_INF, re = -RTR_INF;
             bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
-            if (RTR_REF_KIND(lref) == REF_NODE) lh = slab(q0, q1, r, inv, tmin, le);
-            if (RTR_REF_KIND(rref) == REF_NODE) rh = slab(q2, q3, r, inv, tmin, re);
+            if (RTR_REF_KIND(lref) == REF_NODE) { lh = slab(q0, q1, r, inv, tmin, le); if (COUNT) cnt->nodes++; }
+            if (RTR_REF_KIND(rref) == REF_NODE) { rh = slab(q2, q3, r, inv, tmin, re); if (COUNT) cnt->nodes++; }
             if (!EXHAUSTIVE) {
                 const float lim = cull_limit(best.t);
                 lh = lh && !(le > lim);
