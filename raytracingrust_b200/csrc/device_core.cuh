@@ -93,8 +93,7 @@ struct Counters { uint32_t nodes, tris, spheres, env; };
 // (same IEEE quotient the reference recomputes at every node).  Returns pierced; enter = final tmin.
 struct RayInv { float ix, iy, iz; };
 __device__ __forceinline__ bool slab(const float4& mn, const float4& mx, const Ray& r, const RayInv& inv,
-                                     float tmin, float& enter) {
-    float tmax = RTR_INF;
+                                     float tmin, float tmax, float& enter) {
     float t0 = (mn.x - r.o.x) * inv.ix, t1 = (mx.x - r.o.x) * inv.ix;
     if (inv.ix < 0.0f) { float s = t0; t0 = t1; t1 = s; }
     if (t0 > tmin) tmin = t0;
@@ -177,7 +176,7 @@ __device__ __forceinline__ float cull_limit(float best_t) {
 
 struct StackEntry { uint32_t ref; float enter; };
 
-// Closest hit below `entry` for (tmin, +INF).  NESTED = a volume boundary / mesh sub-query:
+// Closest hit below `entry`; boxes are tested against (tmin, tmax), primitives as the reference does.  NESTED = a volume boundary / mesh sub-query:
 // volume leaves cannot occur there.  Volume leaves of the outer walk are handled by the caller
 // through `on_volume`.
 __device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
@@ -186,7 +185,7 @@ __device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray
 
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const Ray& r, const RayInv& inv,
-                                     float tmin, const RngKey& key, StackEntry* stack, LiteHit& best,
+                                     float tmin, float tmax, const RngKey& key, StackEntry* stack, LiteHit& best,
                                      Counters* cnt) {
     uint32_t cur = entry;
     int sp = 0;
@@ -198,8 +197,8 @@ __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const 
             uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
             float le = -RTR_INF, re = -RTR_INF;
             bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
-            if (RTR_REF_KIND(lref) == REF_NODE) { lh = slab(q0, q1, r, inv, tmin, le); if (COUNT) cnt->nodes++; }
-            if (RTR_REF_KIND(rref) == REF_NODE) { rh = slab(q2, q3, r, inv, tmin, re); if (COUNT) cnt->nodes++; }
+            if (RTR_REF_KIND(lref) == REF_NODE) { lh = slab(q0, q1, r, inv, tmin, tmax, le); if (COUNT) cnt->nodes++; }
+            if (RTR_REF_KIND(rref) == REF_NODE) { rh = slab(q2, q3, r, inv, tmin, tmax, re); if (COUNT) cnt->nodes++; }
             if (!EXHAUSTIVE) {
                 const float lim = cull_limit(best.t);
                 lh = lh && !(le > lim);
@@ -245,8 +244,8 @@ __device__ __forceinline__ bool boundary_t(const SceneView& sc, uint32_t entry, 
     RngKey nokey; nokey.k0 = nokey.k1 = nokey.pixel = nokey.sample = nokey.bounce = 0;
     Counters dummy; dummy.nodes = dummy.tris = dummy.spheres = dummy.env = 0;
     Counters* c = cnt ? cnt : &dummy;
-    if (exhaustive) walk<true, true, true>(sc, entry, r, inv, tmin, nokey, stack, best, c);
-    else walk<false, true, true>(sc, entry, r, inv, tmin, nokey, stack, best, c);
+    if (exhaustive) walk<true, true, true>(sc, entry, r, inv, tmin, RTR_INF, nokey, stack, best, c);
+    else walk<false, true, true>(sc, entry, r, inv, tmin, RTR_INF, nokey, stack, best, c);
     t = best.t;
     return best.ref != REF_EMPTY_VALUE;
 }
@@ -278,7 +277,7 @@ __device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, cons
     RayInv inv; inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z;
     LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
     if (bvh) {
-        walk<EXHAUSTIVE, COUNT, false>(sc, sc.root_entry, r, inv, tmin, key, stack, best, cnt);
+        walk<EXHAUSTIVE, COUNT, false>(sc, sc.root_entry, r, inv, tmin, RTR_INF, key, stack, best, cnt);
         return best;
     }
     float closest = RTR_INF;  // closest_so_far (scene.rs:144)
@@ -296,9 +295,10 @@ __device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, cons
                                  COUNT ? cnt : nullptr);
             if (t == t) { closest = t; best.t = t; best.ref = entry; }
         } else if (kind != REF_EMPTY) {
-            // mesh: its own closest hit, tmax ignored, unconditionally replaces the result (Q9)
+            // mesh: the boxes honour tmax = closest_so_far (bvh.rs:161) but Triangle::hit ignores it
+            // (mesh.rs:151), and any hit returned unconditionally replaces the result (Q9)
             LiteHit m; m.t = RTR_INF; m.ref = REF_EMPTY_VALUE; m.u = m.v = 0.0f;
-            walk<EXHAUSTIVE, COUNT, true>(sc, entry, r, inv, tmin, key, stack, m, cnt);
+            walk<EXHAUSTIVE, COUNT, true>(sc, entry, r, inv, tmin, closest, key, stack, m, cnt);
             if (m.ref != REF_EMPTY_VALUE) { closest = m.t; best = m; }
         }
     }
