@@ -229,6 +229,12 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     v.n_objects = (uint32_t)flat.objects.size();
     v.n_materials = (uint32_t)flat.materials.size();
     v.n_volumes = (uint32_t)flat.volumes.size();
+    v.n_nodes = (uint32_t)(flat.nodes.size() / 4);
+    v.n_sphere_slots = (uint32_t)flat.spheres.size();
+    v.n_tri_slots = (uint32_t)flat.tri_info.size();
+    v.linear_needs_inv = 0;
+    for (const ObjectRec& o : flat.objects)
+        if (RTR_REF_KIND(o.entry) != REF_SPHERE && RTR_REF_KIND(o.entry) != REF_EMPTY) v.linear_needs_inv = 1;
     *out = s;
     return RTR_OK;
 }

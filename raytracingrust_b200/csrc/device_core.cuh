@@ -40,8 +40,11 @@ __device__ __forceinline__ v3 xyz(const float4& q) { return mk(q.x, q.y, q.z); }
 struct Ray { v3 o, d; };
 __device__ __forceinline__ v3 ray_at(const Ray& r, float t) { return r.o + r.d * t; }  // ray.rs:15-17
 
-__device__ __forceinline__ float4 ldg4(const F4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
-__device__ __forceinline__ uint4 ldgu4(const U4* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// Plain (non-__ldg) 128-bit loads: with ld.global.nc nvcc 12.9 was observed to hoist a leaf load above
+// the ref-kind test that guards it (reading spheres[node index], out of bounds) — a plain load may not
+// be speculated.  L1 caches global loads on sm_100 either way.
+__device__ __forceinline__ float4 ldg4(const F4* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ uint4 ldgu4(const U4* p) { return *reinterpret_cast<const uint4*>(p); }
 
 // ------------------------------------------------------------------ Philox4x32-10, keyed draws
 __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
@@ -156,8 +159,8 @@ struct LiteHit {
 // candidate update: min t; among equal t the larger DFS leaf rank wins (bvh.rs:183-187, Q2)
 __device__ __forceinline__ uint32_t leaf_rank(const SceneView& sc, uint32_t ref) {
     uint32_t k = RTR_REF_KIND(ref), i = RTR_REF_INDEX(ref);
-    if (k == REF_SPHERE) return __ldg(&sc.sphere_info[i].w);
-    if (k == REF_TRI) return __ldg(&sc.tri_info[i].w);
+    if (k == REF_SPHERE) return sc.sphere_info[i].w;
+    if (k == REF_TRI) return sc.tri_info[i].w;
     return sc.volumes[i].rank;
 }
 __device__ __forceinline__ void offer(const SceneView& sc, LiteHit& best, float t, uint32_t ref, float u, float v) {
@@ -183,16 +186,38 @@ __device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray
                             float tmin, float tmax, const RngKey& key, StackEntry* stack, bool exhaustive,
                             Counters* cnt);
 
+#define RTR_REF_DONE 0xDFFFFFFFu  // kind 6: traversal finished (never stored in a node)
+
+// pop the next stack entry that survives t-culling
+template <bool EXHAUSTIVE>
+__device__ __forceinline__ uint32_t pop_next(const StackEntry* stack, int& sp, float best_t) {
+    const float lim = cull_limit(best_t);
+    while (sp > 0) {
+        --sp;
+        if (EXHAUSTIVE || !(stack[sp].enter > lim)) return stack[sp].ref;
+    }
+    return RTR_REF_DONE;
+}
+
+// "while-while" traversal: all lanes of a warp first descend interior nodes together, then test
+// their pending leaf together, so node code and leaf code are not serialised against each other.
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const Ray& r, const RayInv& inv,
                                      float tmin, float tmax, const RngKey& key, StackEntry* stack, LiteHit& best,
                                      Counters* cnt) {
     uint32_t cur = entry;
     int sp = 0;
+    if (cur == REF_EMPTY_VALUE) return;
     for (;;) {
-        const uint32_t kind = RTR_REF_KIND(cur);
-        if (kind == REF_NODE) {
+        while (RTR_REF_KIND(cur) == REF_NODE) {
+#ifdef RTR_DEBUG_BOUNDS
+            if (RTR_REF_INDEX(cur) >= sc.n_nodes || sp >= RTR_STACK_CAP - 1) { best.t = -12345.0f; best.ref = cur; best.u = (float)sp; return; }
+#endif
+#ifdef RTR_CLAMP_NODE
+            const F4* q = sc.nodes + (size_t)min(RTR_REF_INDEX(cur), sc.n_nodes - 1) * 4;
+#else
             const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
+#endif
             const float4 q0 = ldg4(q), q1 = ldg4(q + 1), q2 = ldg4(q + 2), q3 = ldg4(q + 3);
             uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
             float le = -RTR_INF, re = -RTR_INF;
@@ -206,34 +231,45 @@ __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const 
             }
             if (lh && rh) {
                 if (re < le) { uint32_t tr = lref; lref = rref; rref = tr; float te = le; le = re; re = te; }
+#ifdef RTR_CLAMP_STACK
+                sp &= 31;
+#endif
                 stack[sp].ref = rref; stack[sp].enter = re; ++sp;
                 cur = lref;
-                continue;
+            } else if (lh) {
+                cur = lref;
+            } else if (rh) {
+                cur = rref;
+            } else {
+                cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
             }
-            if (lh) { cur = lref; continue; }
-            if (rh) { cur = rref; continue; }
-        } else if (kind == REF_SPHERE) {
-            const uint32_t i = RTR_REF_INDEX(cur);
-            float t;
-            if (COUNT) cnt->spheres++;
-            if (sphere_t(ldg4(sc.spheres + i), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
-        } else if (kind == REF_TRI) {
+        }
+        if (cur == RTR_REF_DONE) return;
+        const uint32_t kind = RTR_REF_KIND(cur);
+#ifdef RTR_DEBUG_BOUNDS
+        if ((kind == REF_TRI && RTR_REF_INDEX(cur) >= sc.n_tri_slots) || (kind == REF_SPHERE && RTR_REF_INDEX(cur) >= sc.n_sphere_slots) ||
+            kind > REF_VOLUME) { best.t = -54321.0f; best.ref = cur; best.u = (float)sp; return; }
+#endif
+        if (kind == REF_TRI) {
             const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 3;
             float t, u, v;
             if (COUNT) cnt->tris++;
             if (triangle_t(ldg4(q), ldg4(q + 1), ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
+        } else if (kind == REF_SPHERE) {
+            float t;
+            if (COUNT) cnt->spheres++;
+#ifdef RTR_CLAMP_LEAF
+            if (sphere_t(ldg4(sc.spheres + min(RTR_REF_INDEX(cur), sc.n_sphere_slots - 1)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
+#else
+            if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(cur)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
+#endif
         } else if (!NESTED && kind == REF_VOLUME) {
             const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
             float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack + sp, EXHAUSTIVE, COUNT ? cnt : nullptr);
             if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
         }
-        // pop
-        for (;;) {
-            if (sp == 0) return;
-            --sp;
-            cur = stack[sp].ref;
-            if (EXHAUSTIVE || !(stack[sp].enter > cull_limit(best.t))) break;
-        }
+        cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
+        if (cur == RTR_REF_DONE) return;
     }
 }
 
@@ -274,8 +310,9 @@ __device__ __noinline__ float volume_hit(const SceneView& sc, const VolumeRec& v
 template <bool EXHAUSTIVE, bool COUNT>
 __device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, const Ray& r, float tmin,
                                              const RngKey& key, StackEntry* stack, Counters* cnt) {
-    RayInv inv; inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z;
     LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+    RayInv inv; inv.ix = inv.iy = inv.iz = 0.0f;
+    if (bvh || sc.linear_needs_inv) { inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z; }
     if (bvh) {
         walk<EXHAUSTIVE, COUNT, false>(sc, sc.root_entry, r, inv, tmin, RTR_INF, key, stack, best, cnt);
         return best;
@@ -329,7 +366,7 @@ __device__ __forceinline__ Hit finish_hit(const SceneView& sc, const Ray& r, con
     } else if (kind == REF_TRI) {
         const F4* q = sc.tris + (size_t)i * 3;
         const F4* vn = sc.tri_vn + (size_t)i * 3;
-        const v3 fn = mk(__ldg(&q[0].w), __ldg(&q[1].w), __ldg(&q[2].w));
+        const v3 fn = mk(q[0].w, q[1].w, q[2].w);
         const v3 n0 = xyz(ldg4(vn)), n1 = xyz(ldg4(vn + 1)), n2 = xyz(ldg4(vn + 2));
         const uint4 info = ldgu4(sc.tri_info + i);
         n = lh.u * n1 + lh.v * n2 + (1.0f - lh.u - lh.v) * n0;  // mesh.rs:185
@@ -369,53 +406,76 @@ __device__ __forceinline__ float reflectance(float cosine, float idx) {  // mate
 
 struct Scatter { v3 attenuation; bool some; Ray ray; };
 
-__device__ __forceinline__ Scatter lambertian_scatter(v3 albedo, const Hit& hit, const RngKey& key) {  // :31-41
-    v3 dir = hit.normal + sample_unit_sphere_surface(key);
-    if (near_zero(dir)) dir = hit.normal;
-    Scatter s; s.attenuation = albedo; s.some = true; s.ray.o = hit.point; s.ray.d = dir;
-    return s;
-}
-
-// Material::scatter for Scene.material(handle); MixMaterial unrolled into a loop (materials.rs:150-156)
-__device__ __forceinline__ Scatter scatter(const SceneView& sc, uint32_t material, const Ray& ray, const Hit& hit,
-                                           const RngKey& key) {
-    MaterialRec m = sc.materials[material];
-    for (uint32_t level = 0; m.kind == RTR_MAT_MIX; ++level) {
-        const bool first = gen_range_01(draw(key, P_MIX, level).x) >= m.param;
-        m = sc.materials[first ? m.first : m.second];
+// Material::scatter for Scene.material(handle) (mode Full, render.rs:40) or the fresh
+// Lambertian(0.8) of mode Clay (render.rs:41).
+//
+// Written for SIMT convergence rather than as one function per material: lanes of a warp hold
+// different materials, so everything expensive that several materials share — the Philox draws and
+// the unit-ball rejection loop (sample.rs:44-52) — sits at ONE code site that all lanes needing any
+// draw execute together; the per-material arithmetic afterwards is a few instructions each.
+__device__ __forceinline__ Scatter scatter_event(const SceneView& sc, bool clay, uint32_t material, const Ray& ray,
+                                                 const Hit& hit, const RngKey& key) {
+    uint32_t kind = RTR_MAT_LAMBERTIAN;
+    v3 color = mk(0.8f, 0.8f, 0.8f);
+    float param = 0.0f;
+    if (!clay) {
+        MaterialRec m = sc.materials[material];
+        for (uint32_t level = 0; m.kind == RTR_MAT_MIX; ++level) {  // MixMaterial (materials.rs:150-156)
+            const bool first = gen_range_01(draw(key, P_MIX, level).x) >= m.param;
+            m = sc.materials[first ? m.first : m.second];
+        }
+        kind = m.kind; color = mk(m.r, m.g, m.b); param = m.param;
+    }
+    // Dielectric prologue (materials.rs:114-124)
+    float ratio = 1.0f, cos_theta = 0.0f;
+    v3 unit = mk(0.0f, 0.0f, 0.0f);
+    bool cannot_refract = false;
+    if (kind == RTR_MAT_DIELECTRIC) {
+        ratio = hit.front_face ? 1.0f / param : param;
+        unit = normalize(ray.d);
+        cos_theta = fminf(dot(hit.normal, -unit), 1.0f);
+        const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+        cannot_refract = (ratio * sin_theta) > 1.0f;
+    }
+    // the one draw site: unit-ball rejection for Lambertian / Metal / Isotropic, a single uniform for
+    // a Dielectric that can refract (no draw under total internal reflection, Q11)
+    const bool want_ball = kind == RTR_MAT_LAMBERTIAN || kind == RTR_MAT_METAL || kind == RTR_MAT_ISOTROPIC;
+    const bool want_uniform = kind == RTR_MAT_DIELECTRIC && !cannot_refract;
+    v3 ball = mk(0.0f, 0.0f, 0.0f);
+    float xi = 0.0f;
+    if (want_ball || want_uniform) {
+        const uint32_t purpose = want_ball ? P_SPHERE : P_DIELECTRIC;
+        for (uint32_t k = 0;; ++k) {
+            const uint4 r = draw(key, purpose, k);
+            if (!want_ball) { xi = gen_range_01(r.x); break; }
+            ball = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
+            if (dot(ball, ball) <= 1.0f) break;
+        }
     }
     Scatter s;
     s.ray.o = hit.point;
     s.ray.d = mk(0.0f, 0.0f, 0.0f);
-    const v3 color = mk(m.r, m.g, m.b);
-    switch (m.kind) {
-        case RTR_MAT_LAMBERTIAN: return lambertian_scatter(color, hit, key);
-        case RTR_MAT_METAL: {  // :58-70
-            v3 reflected = normalize(reflect(ray.d, hit.normal));
-            s.ray.d = reflected + m.param * sample_unit_sphere_surface(key);
-            s.some = dot(s.ray.d, hit.normal) > 0.0f;
-            s.attenuation = s.some ? color : mk(0.0f, 0.0f, 0.0f);
-            return s;
-        }
-        case RTR_MAT_EMISSION: s.some = false; s.attenuation = color; return s;  // :88-90
-        case RTR_MAT_DIELECTRIC: {  // :113-138
-            const float ir = m.param;
-            const float ratio = hit.front_face ? 1.0f / ir : ir;
-            const v3 unit = normalize(ray.d);
-            const float cos_theta = fminf(dot(hit.normal, -unit), 1.0f);
-            const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-            const bool cannot_refract = (ratio * sin_theta) > 1.0f;
-            bool refl = cannot_refract;
-            if (!refl) refl = reflectance(cos_theta, ratio) > gen_range_01(draw(key, P_DIELECTRIC, 0).x);
-            s.ray.d = refl ? reflect(unit, hit.normal) : refract(unit, hit.normal, ratio);
-            s.some = true; s.attenuation = mk(1.0f, 1.0f, 1.0f);
-            return s;
-        }
-        default:  // Isotropic (volume.rs:82-87)
-            s.ray.d = sample_unit_sphere_volume(key);
-            s.some = true; s.attenuation = color;
-            return s;
+    s.attenuation = color;
+    s.some = true;
+    if (kind == RTR_MAT_LAMBERTIAN) {  // materials.rs:31-41
+        v3 dir = hit.normal + normalize(ball);
+        if (near_zero(dir)) dir = hit.normal;
+        s.ray.d = dir;
+    } else if (kind == RTR_MAT_METAL) {  // :58-70
+        const v3 reflected = normalize(reflect(ray.d, hit.normal));
+        s.ray.d = reflected + param * normalize(ball);
+        s.some = dot(s.ray.d, hit.normal) > 0.0f;
+        if (!s.some) s.attenuation = mk(0.0f, 0.0f, 0.0f);
+    } else if (kind == RTR_MAT_DIELECTRIC) {  // :125-138
+        const bool refl = cannot_refract || reflectance(cos_theta, ratio) > xi;
+        s.ray.d = refl ? reflect(unit, hit.normal) : refract(unit, hit.normal, ratio);
+        s.attenuation = mk(1.0f, 1.0f, 1.0f);
+    } else if (kind == RTR_MAT_ISOTROPIC) {  // volume.rs:82-87
+        s.ray.d = ball;
+    } else {  // Emission (:88-90)
+        s.some = false;
     }
+    return s;
 }
 
 // ------------------------------------------------------------------ backgrounds (backgrounds.rs)

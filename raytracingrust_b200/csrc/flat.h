@@ -91,6 +91,8 @@ struct SceneView {
     uint32_t n_objects;
     uint32_t n_materials;
     uint32_t n_volumes;
+    uint32_t n_nodes, n_sphere_slots, n_tri_slots;  // array extents (debug bounds checks)
+    uint32_t linear_needs_inv;  // some object is a mesh or a volume (the linear scan then needs 1/d)
 };
 
 }  // namespace rtr

@@ -14,7 +14,7 @@ namespace rtr {
 
 // ------------------------------------------------------------------ megakernel
 template <bool EXHAUSTIVE, bool COUNT>
-__global__ void __launch_bounds__(RTR_MEGA_THREADS) render_megakernel(const RenderArgs a) {
+__global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_megakernel(const RenderArgs a) {
     StackEntry stack[RTR_STACK_CAP];
     const uint32_t lane = threadIdx.x & 31u;
     unsigned long long n_rays = 0, n_nodes = 0, n_tris = 0, n_spheres = 0, n_env = 0;
@@ -64,9 +64,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS) render_megakernel(const Rend
                     } else {
                         const Hit hit = finish_hit(a.sc, ray, lh);
                         if (a.mode == RTR_MODE_FULL || a.mode == RTR_MODE_CLAY) {
-                            const Scatter sc = a.mode == RTR_MODE_FULL
-                                                   ? scatter(a.sc, hit.material, ray, hit, key)                  // :40
-                                                   : lambertian_scatter(mk(0.8f, 0.8f, 0.8f), hit, key);         // :41
+                            const Scatter sc = scatter_event(a.sc, a.mode == RTR_MODE_CLAY, hit.material, ray, hit, key);  // :40-41
                             if (sc.some) {  // attenuation * trace_ray(scattered, depth + 1)  (:51-52)
                                 T = T * sc.attenuation;
                                 ray = sc.ray;
@@ -156,6 +154,14 @@ __global__ void __launch_bounds__(128) trace_batch_kernel(const SceneView sc, co
     Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
     const LiteHit lh = world_hit<EXHAUSTIVE, true>(sc, bvh != 0, r, tmin, key, stack, &cnt);
     rtr_hit h;
+#ifdef RTR_DEBUG_BOUNDS
+    if (lh.t == -12345.0f || lh.t == -54321.0f) {
+        h.object = 0xDEADBEEFu; h.primitive = lh.ref; h.t = lh.t; h.point.x = lh.u; h.point.y = h.point.z = 0.0f;
+        h.normal.x = h.normal.y = h.normal.z = 0.0f; h.front_face = 0; h.material = 0;
+        out[i] = h;
+        return;
+    }
+#endif
     if (lh.ref == REF_EMPTY_VALUE) {
         h.object = RTR_NO_HIT; h.primitive = 0; h.t = 0.0f;
         h.point.x = h.point.y = h.point.z = 0.0f; h.normal.x = h.normal.y = h.normal.z = 0.0f;
@@ -185,8 +191,7 @@ __global__ void scatter_batch_kernel(const SceneView sc, const rtr_scatter_in* i
     h.normal = mk(q.normal.x, q.normal.y, q.normal.z);
     h.t = q.t; h.front_face = q.front_face != 0; h.material = q.material; h.object = 0; h.primitive = 0;
     RngKey key; key.k0 = k0; key.k1 = k1; key.pixel = q.pixel; key.sample = q.sample; key.bounce = q.bounce;
-    const Scatter s = mode == RTR_MODE_CLAY ? lambertian_scatter(mk(0.8f, 0.8f, 0.8f), h, key)
-                                            : scatter(sc, h.material, r, h, key);
+    const Scatter s = scatter_event(sc, mode == RTR_MODE_CLAY, h.material, r, h, key);
     rtr_scatter_out o;
     o.attenuation.x = s.attenuation.x; o.attenuation.y = s.attenuation.y; o.attenuation.z = s.attenuation.z;
     o.scattered = s.some ? 1u : 0u;

@@ -12,6 +12,9 @@
 namespace rtr {
 
 #define RTR_MEGA_THREADS 128
+#ifndef RTR_MEGA_MIN_BLOCKS
+#define RTR_MEGA_MIN_BLOCKS 4  // resident CTAs per SM the register allocation must allow
+#endif
 
 struct v3 { float x, y, z; };
 
