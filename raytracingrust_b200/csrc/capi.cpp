@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -26,6 +27,7 @@ struct rtr_context {
     bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
+    uint32_t refill_threshold = 12;  // tuning knob (RTR_REFILL_THRESHOLD), see DESIGN.md
     uint32_t* work_counter = nullptr;
     unsigned long long* stats = nullptr;  // STAT_COUNT
     // scratch, grown on demand
@@ -133,6 +135,10 @@ rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
     CU(cudaEventCreate(&ctx->ev0));
     CU(cudaEventCreate(&ctx->ev1));
     CU(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (const char* e = std::getenv("RTR_REFILL_THRESHOLD")) {
+        int v = std::atoi(e);
+        ctx->refill_threshold = (uint32_t)(v < 1 ? 1 : v > 32 ? 32 : v);
+    }
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->stats, STAT_COUNT * sizeof(unsigned long long)));
     *out = ctx;
@@ -292,7 +298,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     a.tiles_x = (W + 7) / 8;
     a.n_tiles = a.tiles_x * ((H + 3) / 4);
     // persistent grid: one block per resident slot
-    int per_sm = megakernel_max_blocks_per_sm(exhaustive, count_work);
+    int per_sm = megakernel_max_blocks_per_sm(exhaustive, count_work, p->settings.enable_bvh_tree != 0);
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "megakernel cannot be resident on this device");
     const uint32_t resident_warps = (uint32_t)ctx->sm_count * per_sm * (RTR_MEGA_THREADS / 32);
     // small image + many samples: split the samples of a tile into chunks so the chip is full
@@ -303,6 +309,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
         a.chunk_samples = (count + want - 1) / want;
         a.n_chunks = (count + a.chunk_samples - 1) / a.chunk_samples;
     }
+    a.refill_threshold = ctx->refill_threshold;
     a.accum = accum_dev;
     if (a.n_chunks > 1) {
         CU(grow(&ctx->partials, &ctx->partials_elems, (size_t)a.n_chunks * W * H));

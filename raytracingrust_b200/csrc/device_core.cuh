@@ -199,78 +199,82 @@ __device__ __forceinline__ uint32_t pop_next(const StackEntry* stack, int& sp, f
     return RTR_REF_DONE;
 }
 
-// "while-while" traversal: all lanes of a warp first descend interior nodes together, then test
-// their pending leaf together, so node code and leaf code are not serialised against each other.
+// Traversal is split into two resumable steps over the state (cur, sp, best):
+//   node_step  cur is an interior node: slab-test both children (one 64-B fetch), descend into the
+//              nearer pierced child, push the farther, or pop
+//   leaf_step  cur is a primitive: test it as the reference does, offer the hit, pop
+// cur == RTR_REF_DONE: finished.  Callers schedule the steps: walk() (nested queries, batch kernel)
+// runs the classic "while-while" order; the render kernels pick, per warp, whichever step has more
+// lanes waiting and refill finished lanes in between (kernels.cu, wavefront.cu).
+template <bool EXHAUSTIVE, bool COUNT>
+__device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
+                                          const RayInv& inv, float tmin, float tmax, StackEntry* stack, Counters* cnt) {
+    const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
+    const float4 q0 = ldg4(q), q1 = ldg4(q + 1), q2 = ldg4(q + 2), q3 = ldg4(q + 3);
+    uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
+    float le = -RTR_INF, re = -RTR_INF;
+    bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
+    if (RTR_REF_KIND(lref) == REF_NODE) { lh = slab(q0, q1, r, inv, tmin, tmax, le); if (COUNT) cnt->nodes++; }
+    if (RTR_REF_KIND(rref) == REF_NODE) { rh = slab(q2, q3, r, inv, tmin, tmax, re); if (COUNT) cnt->nodes++; }
+    if (!EXHAUSTIVE) {
+        const float lim = cull_limit(best.t);
+        lh = lh && !(le > lim);
+        rh = rh && !(re > lim);
+    }
+    if (lh && rh) {
+        if (re < le) { uint32_t tr = lref; lref = rref; rref = tr; float te = le; le = re; re = te; }
+        stack[sp].ref = rref; stack[sp].enter = re; ++sp;
+        cur = lref;
+    } else if (lh) {
+        cur = lref;
+    } else if (rh) {
+        cur = rref;
+    } else {
+        cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
+    }
+}
+
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
+__device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
+                                          const RayInv& inv, float tmin, const RngKey& key, StackEntry* stack,
+                                          Counters* cnt) {
+    const uint32_t kind = RTR_REF_KIND(cur);
+    if (kind == REF_TRI) {
+        const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 3;
+        float t, u, v;
+        if (COUNT) cnt->tris++;
+        if (triangle_t(ldg4(q), ldg4(q + 1), ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
+    } else if (kind == REF_SPHERE) {
+        float t;
+        if (COUNT) cnt->spheres++;
+        if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(cur)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
+    } else if (!NESTED && kind == REF_VOLUME) {
+        const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
+        float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack + sp, EXHAUSTIVE, COUNT ? cnt : nullptr);
+        if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
+    }
+    cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
+}
+
+// one "while-while" round: all lanes descend interior nodes together, then test their pending leaf together
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
+__device__ __forceinline__ void walk_round(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
+                                           const RayInv& inv, float tmin, float tmax, const RngKey& key,
+                                           StackEntry* stack, Counters* cnt) {
+    while (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(sc, cur, sp, best, r, inv, tmin, tmax, stack, cnt);
+    if (cur == RTR_REF_DONE) return;
+    leaf_step<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
+}
+
+__device__ __forceinline__ uint32_t walk_entry(uint32_t entry) { return entry == REF_EMPTY_VALUE ? RTR_REF_DONE : entry; }
+
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const Ray& r, const RayInv& inv,
                                      float tmin, float tmax, const RngKey& key, StackEntry* stack, LiteHit& best,
                                      Counters* cnt) {
-    uint32_t cur = entry;
+    uint32_t cur = walk_entry(entry);
     int sp = 0;
-    if (cur == REF_EMPTY_VALUE) return;
-    for (;;) {
-        while (RTR_REF_KIND(cur) == REF_NODE) {
-#ifdef RTR_DEBUG_BOUNDS
-            if (RTR_REF_INDEX(cur) >= sc.n_nodes || sp >= RTR_STACK_CAP - 1) { best.t = -12345.0f; best.ref = cur; best.u = (float)sp; return; }
-#endif
-#ifdef RTR_CLAMP_NODE
-            const F4* q = sc.nodes + (size_t)min(RTR_REF_INDEX(cur), sc.n_nodes - 1) * 4;
-#else
-            const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
-#endif
-            const float4 q0 = ldg4(q), q1 = ldg4(q + 1), q2 = ldg4(q + 2), q3 = ldg4(q + 3);
-            uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
-            float le = -RTR_INF, re = -RTR_INF;
-            bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
-            if (RTR_REF_KIND(lref) == REF_NODE) { lh = slab(q0, q1, r, inv, tmin, tmax, le); if (COUNT) cnt->nodes++; }
-            if (RTR_REF_KIND(rref) == REF_NODE) { rh = slab(q2, q3, r, inv, tmin, tmax, re); if (COUNT) cnt->nodes++; }
-            if (!EXHAUSTIVE) {
-                const float lim = cull_limit(best.t);
-                lh = lh && !(le > lim);
-                rh = rh && !(re > lim);
-            }
-            if (lh && rh) {
-                if (re < le) { uint32_t tr = lref; lref = rref; rref = tr; float te = le; le = re; re = te; }
-#ifdef RTR_CLAMP_STACK
-                sp &= 31;
-#endif
-                stack[sp].ref = rref; stack[sp].enter = re; ++sp;
-                cur = lref;
-            } else if (lh) {
-                cur = lref;
-            } else if (rh) {
-                cur = rref;
-            } else {
-                cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
-            }
-        }
-        if (cur == RTR_REF_DONE) return;
-        const uint32_t kind = RTR_REF_KIND(cur);
-#ifdef RTR_DEBUG_BOUNDS
-        if ((kind == REF_TRI && RTR_REF_INDEX(cur) >= sc.n_tri_slots) || (kind == REF_SPHERE && RTR_REF_INDEX(cur) >= sc.n_sphere_slots) ||
-            kind > REF_VOLUME) { best.t = -54321.0f; best.ref = cur; best.u = (float)sp; return; }
-#endif
-        if (kind == REF_TRI) {
-            const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 3;
-            float t, u, v;
-            if (COUNT) cnt->tris++;
-            if (triangle_t(ldg4(q), ldg4(q + 1), ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
-        } else if (kind == REF_SPHERE) {
-            float t;
-            if (COUNT) cnt->spheres++;
-#ifdef RTR_CLAMP_LEAF
-            if (sphere_t(ldg4(sc.spheres + min(RTR_REF_INDEX(cur), sc.n_sphere_slots - 1)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
-#else
-            if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(cur)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
-#endif
-        } else if (!NESTED && kind == REF_VOLUME) {
-            const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
-            float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack + sp, EXHAUSTIVE, COUNT ? cnt : nullptr);
-            if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
-        }
-        cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
-        if (cur == RTR_REF_DONE) return;
-    }
+    while (cur != RTR_REF_DONE) walk_round<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, tmax, key, stack, cnt);
 }
 
 // boundary.hit(ray, tmin, +INF) of a volume boundary: only t is consumed (volume.rs:36-37)

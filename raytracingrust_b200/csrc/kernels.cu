@@ -13,89 +13,141 @@
 namespace rtr {
 
 // ------------------------------------------------------------------ megakernel
-template <bool EXHAUSTIVE, bool COUNT>
+// Lane = pixel (samples of a pixel are traced and summed in order, render.rs:86-100, so the image is
+// bit-reproducible); a warp = an 8x4 pixel tile.  Each lane runs a small path state machine
+//     FRESH (camera ray) -> LAUNCH (start world.hit) -> [walk rounds] -> SHADE (scatter / terminate) -> ...
+// The BVH walk is resumable (walk_round), which lets the warp REFILL lanes: when fewer than
+// `refill_threshold` lanes are still walking, the lanes whose walk has finished shade their hit and
+// start their next ray while the others keep their traversal state, instead of idling until the
+// longest walk of the warp ends (ncu before this: 4.3 of 32 lanes active in the node loop on the mesh scene).
+enum { ST_FRESH = 0, ST_LAUNCH = 1, ST_SHADE = 2, ST_DEAD = 3 };
+
+template <bool EXHAUSTIVE, bool COUNT, bool BVH>
 __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_megakernel(const RenderArgs a) {
     StackEntry stack[RTR_STACK_CAP];
     const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t FULL = 0xffffffffu;
     unsigned long long n_rays = 0, n_nodes = 0, n_tris = 0, n_spheres = 0, n_env = 0;
+    const bool bvh = BVH;  // settings.enable_bvh_tree (render.rs:68-72); false = linear scan, no resumable walk
 
     for (;;) {
         uint32_t item = 0;
         if (lane == 0) item = atomicAdd(a.work_counter, 1u);
-        item = __shfl_sync(0xffffffffu, item, 0);
+        item = __shfl_sync(FULL, item, 0);
         if (item >= a.n_tiles * a.n_chunks) break;
         const uint32_t tile = item / a.n_chunks, chunk = item - tile * a.n_chunks;
         const uint32_t tx = tile % a.tiles_x, ty = tile / a.tiles_x;
         const uint32_t x = tx * 8u + (lane & 7u), y = ty * 4u + (lane >> 3);
-        if (x < a.width && y < a.height) {
-            const uint32_t pixel = y * a.width + x;  // index = y*W + x (render.rs:76-77)
-            uint32_t s = a.sample_begin + chunk * a.chunk_samples;
-            const uint32_t s_last = a.sample_begin + a.sample_count;
-            const uint32_t s_end = min(s + a.chunk_samples, s_last);
-            Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
-            uint32_t rays = 0;
-            v3 sum = mk(0.0f, 0.0f, 0.0f);
-            RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = pixel; key.sample = s; key.bounce = 0;
-            Ray ray; ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
-            v3 T = mk(1.0f, 1.0f, 1.0f);
-            uint32_t depth = 0;
-            bool fresh = true;
-            for (;;) {
-                if (fresh) {
-                    if (s >= s_end) break;
-                    key.sample = s; key.bounce = 0;
-                    ray = camera_sample_ray(a.cam, a.width, a.height, x, y, key);  // render.rs:88-92
-                    T = mk(1.0f, 1.0f, 1.0f);
-                    depth = 0;
-                    fresh = false;
-                }
-                // one trace_ray frame (render.rs:32-59); L = radiance when the path ends here
-                v3 L;
-                bool done = true;
-                if (depth >= a.max_ray_depth) {
-                    L = T * mk(0.0f, 0.0f, 0.0f);
-                } else {
-                    key.bounce = depth;
-                    ++rays;
-                    const LiteHit lh = world_hit<EXHAUSTIVE, COUNT>(a.sc, a.enable_bvh_tree != 0, ray, 0.00001f, key,
-                                                                    stack, &cnt);
-                    if (lh.ref == REF_EMPTY_VALUE) {
+        const bool valid = x < a.width && y < a.height;
+        const uint32_t pixel = y * a.width + x;  // index = y*W + x (render.rs:76-77)
+        uint32_t s = a.sample_begin + chunk * a.chunk_samples;
+        const uint32_t s_first = s;
+        const uint32_t s_end = min(s + a.chunk_samples, a.sample_begin + a.sample_count);
+        Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
+        uint32_t rays = 0;
+        v3 sum = mk(0.0f, 0.0f, 0.0f);
+        RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = pixel; key.sample = s; key.bounce = 0;
+        Ray ray; ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
+        RayInv inv; inv.ix = inv.iy = inv.iz = 0.0f;
+        v3 T = mk(1.0f, 1.0f, 1.0f);
+        uint32_t depth = 0;
+        uint32_t state = valid ? ST_FRESH : ST_DEAD;
+        bool walking = false;
+        uint32_t cur = RTR_REF_DONE;
+        int sp = 0;
+        LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+
+        for (;;) {
+            // ---- lanes without a walk in flight: shade what they found, start their next ray
+            while (state != ST_DEAD && !walking) {
+                v3 L = mk(0.0f, 0.0f, 0.0f);
+                bool finished = false;  // this sample's radiance L is final
+                if (state == ST_SHADE) {  // the rest of one trace_ray frame (render.rs:39-57)
+                    if (best.ref == REF_EMPTY_VALUE) {
                         L = T * background_sample(a.sc, ray, COUNT ? &cnt : nullptr);  // :57
+                        finished = true;
                     } else {
-                        const Hit hit = finish_hit(a.sc, ray, lh);
+                        const Hit hit = finish_hit(a.sc, ray, best);
                         if (a.mode == RTR_MODE_FULL || a.mode == RTR_MODE_CLAY) {
                             const Scatter sc = scatter_event(a.sc, a.mode == RTR_MODE_CLAY, hit.material, ray, hit, key);  // :40-41
                             if (sc.some) {  // attenuation * trace_ray(scattered, depth + 1)  (:51-52)
                                 T = T * sc.attenuation;
                                 ray = sc.ray;
                                 ++depth;
-                                done = false;
+                                state = ST_LAUNCH;
                             } else {
                                 L = T * sc.attenuation;  // :54
+                                finished = true;
                             }
                         } else if (a.mode == RTR_MODE_NORMAL) {  // :42-45
                             L = T * (0.5f * (normalize(hit.normal) + mk(1.0f, 1.0f, 1.0f)));
+                            finished = true;
                         } else {
                             L = T * mk(0.0f, 0.0f, 0.0f);  // Random (:46-48)
+                            finished = true;
                         }
                     }
+                } else if (state == ST_LAUNCH) {  // only reached with depth >= max_ray_depth (:34-36)
+                    L = T * mk(0.0f, 0.0f, 0.0f);
+                    finished = true;
                 }
-                if (done) {
+                if (finished) {
                     L.x = f32_clamp(L.x, 0.0f, a.clamp_indirect);  // render.rs:95-97
                     L.y = f32_clamp(L.y, 0.0f, a.clamp_indirect);
                     L.z = f32_clamp(L.z, 0.0f, a.clamp_indirect);
                     sum = sum + L;  // :99
                     ++s;
-                    fresh = true;
+                    state = ST_FRESH;
+                }
+                if (state == ST_FRESH) {
+                    if (s >= s_end) { state = ST_DEAD; break; }
+                    key.sample = s; key.bounce = 0;
+                    ray = camera_sample_ray(a.cam, a.width, a.height, x, y, key);  // render.rs:88-92
+                    T = mk(1.0f, 1.0f, 1.0f);
+                    depth = 0;
+                    state = ST_LAUNCH;
+                }
+                // state == ST_LAUNCH: world.hit(ray, 0.00001, INF) (:38) unless the depth limit ends the path
+                if (depth >= a.max_ray_depth) continue;
+                key.bounce = depth;
+                ++rays;
+                state = ST_SHADE;
+                if (bvh) {
+                    inv.ix = 1.0f / ray.d.x; inv.iy = 1.0f / ray.d.y; inv.iz = 1.0f / ray.d.z;
+                    best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+                    cur = walk_entry(a.sc.root_entry);
+                    sp = 0;
+                    walking = cur != RTR_REF_DONE;
+                } else {
+                    best = world_hit<EXHAUSTIVE, COUNT>(a.sc, false, ray, 0.00001f, key, stack, &cnt);
                 }
             }
-            const uint32_t first = a.sample_begin + chunk * a.chunk_samples;
-            const float n = first < s_end ? (float)(s_end - first) : 0.0f;
+            const uint32_t alive = __ballot_sync(FULL, state != ST_DEAD);
+            if (!BVH || alive == 0u) break;
+            const uint32_t keep = min(a.refill_threshold, (uint32_t)__popc(alive));
+            // ---- walk until enough lanes have finished to make a refill worth its divergence.  Each turn
+            // runs whichever step has more lanes waiting (majority rule): node steps while at least as
+            // many lanes sit at interior nodes as at primitives, then one primitive step for the rest.
+            do {
+                for (;;) {
+                    const bool at_node = RTR_REF_KIND(cur) == REF_NODE;
+                    const uint32_t mn = __ballot_sync(FULL, at_node);
+                    const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
+                    if (mn == 0u || __popc(mn) < __popc(ml)) break;
+                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, ray, inv, 0.00001f, RTR_INF, stack, &cnt);
+                }
+                if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
+                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, ray, inv, 0.00001f, key, stack, &cnt);
+            } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
+            walking = cur != RTR_REF_DONE;
+        }
+        if (valid) {
+            const float n = s_first < s_end ? (float)(s_end - s_first) : 0.0f;
             float4* dst = a.n_chunks == 1 ? a.accum : a.partials + (size_t)chunk * a.width * a.height;
             dst[pixel] = make_float4(sum.x, sum.y, sum.z, n);
-            n_rays += rays;
-            if (COUNT) { n_nodes += cnt.nodes; n_tris += cnt.tris; n_spheres += cnt.spheres; n_env += cnt.env; }
         }
+        n_rays += rays;
+        if (COUNT) { n_nodes += cnt.nodes; n_tris += cnt.tris; n_spheres += cnt.spheres; n_env += cnt.env; }
     }
     // per-warp reduction of the counters, one atomic per warp and counter
 #pragma unroll
@@ -222,24 +274,32 @@ __global__ void camera_rays_kernel(const CameraBasis cam, uint32_t W, uint32_t H
 }
 
 // ------------------------------------------------------------------ launchers (called from capi.cpp)
-int megakernel_max_blocks_per_sm(bool exhaustive, bool count) {
+template <typename F>
+static auto pick_megakernel(bool exhaustive, bool count, bool bvh, F f) {
+#define RTR_PICK(E, C, B) return f(render_megakernel<E, C, B>)
+    if (exhaustive) {
+        if (count) { if (bvh) RTR_PICK(true, true, true); else RTR_PICK(true, true, false); }
+        else { if (bvh) RTR_PICK(true, false, true); else RTR_PICK(true, false, false); }
+    } else {
+        if (count) { if (bvh) RTR_PICK(false, true, true); else RTR_PICK(false, true, false); }
+        else { if (bvh) RTR_PICK(false, false, true); else RTR_PICK(false, false, false); }
+    }
+#undef RTR_PICK
+}
+
+int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh) {
     int n = 0;
-    cudaError_t e;
-    if (exhaustive) e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_megakernel<true, true>, RTR_MEGA_THREADS, 0)
-                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_megakernel<true, false>, RTR_MEGA_THREADS, 0);
-    else e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_megakernel<false, true>, RTR_MEGA_THREADS, 0)
-                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, render_megakernel<false, false>, RTR_MEGA_THREADS, 0);
+    cudaError_t e = pick_megakernel(exhaustive, count, bvh, [&](void (*k)(const RenderArgs)) {
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_MEGA_THREADS, 0);
+    });
     return e == cudaSuccess ? n : 0;
 }
 
 cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st) {
-    if (exhaustive) {
-        if (count) render_megakernel<true, true><<<grid, RTR_MEGA_THREADS, 0, st>>>(a);
-        else render_megakernel<true, false><<<grid, RTR_MEGA_THREADS, 0, st>>>(a);
-    } else {
-        if (count) render_megakernel<false, true><<<grid, RTR_MEGA_THREADS, 0, st>>>(a);
-        else render_megakernel<false, false><<<grid, RTR_MEGA_THREADS, 0, st>>>(a);
-    }
+    pick_megakernel(exhaustive, count, a.enable_bvh_tree != 0, [&](void (*k)(const RenderArgs)) {
+        k<<<grid, RTR_MEGA_THREADS, 0, st>>>(a);
+        return cudaSuccess;
+    });
     return cudaGetLastError();
 }
 

@@ -35,13 +35,14 @@ struct RenderArgs {
     uint32_t sample_begin, sample_count;
     uint32_t tiles_x, n_tiles;   // 8x4-pixel warp tiles
     uint32_t n_chunks, chunk_samples;  // sample chunks per tile (1 unless the image is small)
+    uint32_t refill_threshold;   // 1..32: refill finished lanes once fewer than this many are still walking
     float4* accum;               // W*H: (sum r, sum g, sum b, samples)
     float4* partials;            // n_chunks * W*H when n_chunks > 1
     uint32_t* work_counter;      // zeroed before launch
     unsigned long long* stats;   // STAT_COUNT counters
 };
 
-int megakernel_max_blocks_per_sm(bool exhaustive, bool count);
+int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh);
 cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
 cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, cudaStream_t st);
 cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels, float spp, cudaStream_t st);
@@ -54,6 +55,49 @@ cudaError_t launch_background_batch(const SceneView& sc, const rtr_ray* rays, si
 cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, uint32_t k0, uint32_t k1,
                                const uint32_t* pixels, const uint32_t* samples, size_t n, rtr_ray* out,
                                cudaStream_t st);
+
+// ------------------------------------------------------------------ wavefront variant (wavefront.cu)
+// One WAVE = `wave_samples` consecutive global samples of every pixel, traced to completion:
+//   wf_generate -> [ wf_extend -> wf_shade(+compact) ] x max_ray_depth -> (wf_sum_samples)
+// Path state lives in HBM as SoA float4 streams, double-buffered so that wf_shade writes the
+// surviving paths DENSELY (warp ballot + popc + one atomic per warp) into the other buffer.
+#define RTR_WF_THREADS 128
+#define RTR_WF_MAX_DEPTH 256      // max_ray_depth is a u8 in the reference
+enum { WFC_WAVE = 0, WFC_QCOUNT = 8, WFC_FETCH = WFC_QCOUNT + RTR_WF_MAX_DEPTH + 8, WFC_WORDS = WFC_FETCH + RTR_WF_MAX_DEPTH + 8 };
+
+struct WfPaths {      // one path per slot
+    float4* o;        // ray origin.xyz, w = bits(pixel index)
+    float4* d;        // ray direction.xyz, w = bits((sample - wave_begin) << 8 | depth)
+    float4* thr;      // throughput T.xyz (product of attenuations so far), w unused
+};
+
+struct WfArgs {
+    SceneView sc;
+    CameraBasis cam;
+    uint32_t width, height, n_pixels;
+    uint32_t max_ray_depth;
+    float clamp_indirect;
+    uint32_t enable_bvh_tree;
+    uint32_t mode;
+    uint32_t k0, k1;
+    uint32_t sample_begin, sample_end;  // this call's global sample range
+    uint32_t wave_samples;              // samples of every pixel in flight per wave
+    uint32_t bounce;                    // which [extend, shade] pair this launch is
+    uint32_t refill_threshold;          // extend refills idle lanes when fewer lanes than this are walking
+    WfPaths in, out;
+    float4* hit;                        // per slot of `in`: (t, bits(ref), u, v)
+    float4* accum;                      // W*H (sum r, sum g, sum b, samples)
+    float4* lbuf;                       // wave_samples * n_pixels clamped sample radiances (wave_samples > 1)
+    uint32_t* counters;                 // WFC_WORDS words, see enum
+    unsigned long long* stats;
+};
+
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count);
+cudaError_t launch_wf_begin(const WfArgs& a, cudaStream_t st);       // zero accum + wave counter
+cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st);
+cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
+cudaError_t launch_wf_shade(const WfArgs& a, int grid, bool count, cudaStream_t st);
+cudaError_t launch_wf_end_wave(const WfArgs& a, int grid, cudaStream_t st);  // ordered sum of lbuf + advance the wave
 
 }  // namespace rtr
 #endif
