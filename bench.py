@@ -251,15 +251,17 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "msamples_per_s": samples_step * args.steps / (ms * 1e-3) / 1e6,
             "rays_per_step": rays_step, "samples_per_step": samples_step,
-            "config": {"workload": desc, "kernel": "megakernel", "per_gpu_spp": spp, "parallelism": f"sample-slices x{world} + ncclReduce",
+            "config": {"workload": desc, "kernel": {1: "megakernel", 2: "wavefront"}[st_count["kernel_used"]], "per_gpu_spp": spp, "parallelism": f"sample-slices x{world} + ncclReduce",
                        "l2_policy": "each step rewrites the 33 MB accumulation buffer and traces fresh Philox paths; scene working set is L2-resident by design (SURVEY 8d)",
                        "scene_device_bytes": info["device_bytes"], "bvh_nodes": info["n_nodes"]},
             "clocks": clocks,
             "e2e": {"value": rays_step * e2e_steps / e2e_s / 1e6, "unit": "Mrays/s",
                     "h2d_bytes_per_step": info["h2d_bytes"], "d2h_bytes_per_step": W * H * 4 + 64, "steps": e2e_steps},
-            "gpu_launches": args.steps * 2,  # render_megakernel + resolve_kernel per step (NCCL's reduce kernel is not ours)
+            # our kernels per step: the render kernels (megakernel, or the wavefront's per-wave sequence) + resolve_kernel
+            # (NCCL's reduce kernel is not ours)
+            "gpu_launches": args.steps * (st_count["kernel_launches"] + 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "kernel": "render_megakernel",
+                         "traffic": traffic, "peak_source": peak_src, "kernel": "render_megakernel" if st_count["kernel_used"] == 1 else "wavefront wave sequence (wf_extend dominant)",
                          "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                          "bytes_per_ray": alg / max(st_count["rays"], 1),
                          "note": "scene is L2-resident: the binding limit is SM issue/latency, not HBM (DESIGN.md)"},

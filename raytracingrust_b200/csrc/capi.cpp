@@ -34,6 +34,11 @@ struct rtr_context {
     float4* accum = nullptr; size_t accum_pixels = 0;
     float4* partials = nullptr; size_t partials_elems = 0;
     uchar4* rgba = nullptr; size_t rgba_pixels = 0;
+    float4* wf_state = nullptr; size_t wf_state_elems = 0;  // wavefront: 7 path streams (+ lbuf), see render_wavefront
+    uint32_t* wf_counters = nullptr;
+    uint32_t wf_refill_threshold = 24;  // RTR_WF_REFILL_THRESHOLD
+    uint64_t wf_target_paths = 1ull << 21;  // RTR_WF_PATHS: paths in flight per wave
+    int wf_use_graph = 1;  // RTR_WF_GRAPH
     char* batch_in = nullptr; size_t batch_in_bytes = 0;
     char* batch_in2 = nullptr; size_t batch_in2_bytes = 0;
     char* batch_out = nullptr; size_t batch_out_bytes = 0;
@@ -139,7 +144,17 @@ rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
         int v = std::atoi(e);
         ctx->refill_threshold = (uint32_t)(v < 1 ? 1 : v > 32 ? 32 : v);
     }
+    if (const char* e = std::getenv("RTR_WF_REFILL_THRESHOLD")) {
+        int v = std::atoi(e);
+        ctx->wf_refill_threshold = (uint32_t)(v < 1 ? 1 : v > 32 ? 32 : v);
+    }
+    if (const char* e = std::getenv("RTR_WF_PATHS")) {
+        long long v = std::atoll(e);
+        if (v >= 1024) ctx->wf_target_paths = (uint64_t)v;
+    }
+    if (const char* e = std::getenv("RTR_WF_GRAPH")) ctx->wf_use_graph = std::atoi(e);
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
+    CU(cudaMalloc((void**)&ctx->wf_counters, WFC_WORDS * sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->stats, STAT_COUNT * sizeof(unsigned long long)));
     *out = ctx;
     return RTR_OK;
@@ -149,6 +164,7 @@ void rtr_context_destroy(rtr_context* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    cudaFree(ctx->wf_state); cudaFree(ctx->wf_counters);
     cudaFree(ctx->work_counter); cudaFree(ctx->stats); cudaFree(ctx->accum); cudaFree(ctx->partials);
     cudaFree(ctx->rgba); cudaFree(ctx->batch_in); cudaFree(ctx->batch_in2); cudaFree(ctx->batch_out);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -277,9 +293,125 @@ static rtr_status check_render_args(rtr_context* ctx, const rtr_scene* scene, co
     return RTR_OK;
 }
 
+// ------------------------------------------------------------------ wavefront variant (wavefront.cu)
+// One wave = generate, max_ray_depth x [extend, shade+compact], ordered sample sum, next-wave bookkeeping.
+// Every queue size lives on the device, so the launch sequence of a wave is fixed: it is captured into a
+// CUDA graph once per call and replayed for each wave (falls back to plain launches if capture fails).
+static cudaError_t wf_launch_wave(rtr_context* ctx, WfArgs a, const WfPaths buf[2], bool exhaustive, bool count_work,
+                                  int gen_grid, int ext_grid, int shade_grid, int sum_grid, uint32_t* launches) {
+    cudaError_t e = cudaSuccess;
+    auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; ++*launches; };
+    a.bounce = 0; a.in = buf[0]; a.out = buf[1];
+    step(launch_wf_generate(a, gen_grid, ctx->stream));
+    for (uint32_t b = 0; b < a.max_ray_depth; ++b) {
+        a.bounce = b; a.in = buf[b & 1]; a.out = buf[(b + 1) & 1];
+        step(launch_wf_extend(a, ext_grid, exhaustive, count_work, ctx->stream));
+        step(launch_wf_shade(a, shade_grid, count_work, ctx->stream));
+    }
+    step(launch_wf_end_wave(a, sum_grid, ctx->stream));
+    if (a.lbuf) ++*launches;
+    return e;
+}
+
+static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
+                                   float4* accum_dev, bool timed, rtr_stats* stats_out) {
+    const uint32_t W = p->width, H = p->height;
+    const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
+    const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;
+    const bool count_work = stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0;
+    const uint64_t n_pixels = (uint64_t)W * H;
+    WfArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.sc = scene->view;
+    a.cam = ray_origin(p->camera);
+    a.width = W; a.height = H; a.n_pixels = (uint32_t)n_pixels;
+    a.max_ray_depth = p->settings.max_ray_depth;
+    a.clamp_indirect = p->settings.clamp_indirect;
+    a.enable_bvh_tree = p->settings.enable_bvh_tree;
+    a.mode = p->settings.mode;
+    a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
+    a.sample_begin = p->sample_begin; a.sample_end = p->sample_begin + count;
+    a.refill_threshold = ctx->wf_refill_threshold;
+    // samples of every pixel in flight per wave: enough paths to fill the chip, bounded scratch
+    uint64_t ws = n_pixels ? ctx->wf_target_paths / n_pixels : 1;
+    if (ws < 1) ws = 1;
+    if (ws > count) ws = count ? count : 1;
+    if (ws > 0xFFFFFFull) ws = 0xFFFFFFull;  // (sample - wave_begin) is packed into 24 bits
+    a.wave_samples = (uint32_t)ws;
+    const uint64_t n_paths = ws * n_pixels;
+    if (n_paths > 0x7FFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "wavefront: too many paths per wave");
+    const uint32_t n_waves = count ? (uint32_t)((count + ws - 1) / ws) : 0;
+    const bool use_lbuf = ws > 1;
+    const size_t streams = 7 + (use_lbuf ? 1 : 0);
+    CU(grow(&ctx->wf_state, &ctx->wf_state_elems, streams * (size_t)n_paths));
+    WfPaths buf[2];
+    float4* s0 = ctx->wf_state;
+    buf[0].o = s0; buf[0].d = s0 + n_paths; buf[0].thr = s0 + 2 * n_paths;
+    buf[1].o = s0 + 3 * n_paths; buf[1].d = s0 + 4 * n_paths; buf[1].thr = s0 + 5 * n_paths;
+    a.hit = s0 + 6 * n_paths;
+    a.lbuf = use_lbuf ? s0 + 7 * n_paths : nullptr;
+    a.accum = accum_dev;
+    a.counters = ctx->wf_counters;
+    a.stats = ctx->stats;
+    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work);
+    if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
+    auto blocks_for = [&](uint64_t items, int cap_per_sm) {
+        uint64_t b = (items + RTR_WF_THREADS - 1) / RTR_WF_THREADS;
+        const uint64_t cap = (uint64_t)ctx->sm_count * cap_per_sm;
+        return (int)(b < 1 ? 1 : b > cap ? cap : b);
+    };
+    const int ext_grid = blocks_for(n_paths, per_sm);
+    const int gen_grid = blocks_for(n_paths + 32 * (uint64_t)ws * (W / 8 + H / 4 + 2), 16);
+    const int shade_grid = blocks_for(n_paths, 16);
+    const int sum_grid = blocks_for(n_pixels, 8);
+    CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
+    uint32_t launches = 0;
+    if (timed) CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    CU(launch_wf_begin(a, ctx->stream));
+    ++launches;
+    bool done = false;
+    if (ctx->wf_use_graph && n_waves > 1) {
+        cudaGraph_t graph = nullptr;
+        cudaGraphExec_t exec = nullptr;
+        uint32_t per_wave = 0;
+        cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
+        if (e == cudaSuccess) {
+            cudaError_t le = wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, &per_wave);
+            e = cudaStreamEndCapture(ctx->stream, &graph);
+            if (e == cudaSuccess && le != cudaSuccess) e = le;
+        }
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (e == cudaSuccess) {
+            for (uint32_t w = 0; w < n_waves && e == cudaSuccess; ++w) e = cudaGraphLaunch(exec, ctx->stream);
+            launches += per_wave * n_waves;
+            done = e == cudaSuccess;
+        }
+        if (exec) cudaGraphExecDestroy(exec);
+        if (graph) cudaGraphDestroy(graph);
+        if (!done) {
+            (void)cudaGetLastError();
+            if (e != cudaSuccess && e != cudaErrorStreamCaptureUnsupported && e != cudaErrorNotSupported)
+                return cuda_fail(ctx, e, "wavefront graph");
+            return fail(ctx, RTR_CUDA_ERROR, "wavefront: CUDA graph capture unavailable on this stream (set RTR_WF_GRAPH=0)");
+        }
+    }
+    if (!done)
+        for (uint32_t w = 0; w < n_waves; ++w)
+            CU(wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, &launches));
+    if (timed) CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    if (stats_out) {
+        std::memset(stats_out, 0, sizeof(*stats_out));
+        stats_out->kernel_launches = launches;
+        stats_out->kernel_used = RTR_KERNEL_WAVEFRONT;
+        stats_out->samples = n_pixels * count;
+    }
+    return RTR_OK;
+}
+
 // launches the render kernels for this call's sample slice into accum_dev; fills stats (async)
 static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
                               float4* accum_dev, bool timed, rtr_stats* stats_out) {
+    if (p->kernel == RTR_KERNEL_WAVEFRONT) return render_wavefront(ctx, scene, p, accum_dev, timed, stats_out);
     const uint32_t W = p->width, H = p->height;
     const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
     const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;

@@ -19,7 +19,7 @@ namespace rtr {
 #define RTR_PI 3.14159265358979323846f  // std::f32::consts::PI (types.rs:5)
 #define RTR_STACK_CAP 48                // (ref, enter) pairs per thread; host checks max depth
 
-// ------------------------------------------------------------------ vectors (cgmath 0.18 order)
+// ------------------------------------------------------------------ vectors (cgmath 0.18 order)  [bucket:vecmath]
 // struct v3 { float x, y, z; } comes from kernels.h
 __device__ __forceinline__ v3 mk(float x, float y, float z) { v3 r; r.x = x; r.y = y; r.z = z; return r; }
 __device__ __forceinline__ v3 operator+(v3 a, v3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
@@ -46,7 +46,7 @@ __device__ __forceinline__ v3 ray_at(const Ray& r, float t) { return r.o + r.d *
 __device__ __forceinline__ float4 ldg4(const F4* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ uint4 ldgu4(const U4* p) { return *reinterpret_cast<const uint4*>(p); }
 
-// ------------------------------------------------------------------ Philox4x32-10, keyed draws
+// ------------------------------------------------------------------ Philox4x32-10, keyed draws  [bucket:rng]
 __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
                                                uint32_t k0, uint32_t k1) {
     const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
@@ -87,10 +87,10 @@ __device__ __forceinline__ v3 sample_unit_sphere_surface(const RngKey& key) {  /
     return normalize(sample_unit_sphere_volume(key));
 }
 
-// ------------------------------------------------------------------ work counters (optional)
+// ------------------------------------------------------------------ work counters (optional)  [bucket:other]
 struct Counters { uint32_t nodes, tris, spheres, env; };
 
-// ------------------------------------------------------------------ AABB::hit (aabb.rs:81-137)
+// ------------------------------------------------------------------ AABB::hit (aabb.rs:81-137)  [bucket:slab]
 // Same t0/t1/swap/update sequence; the per-axis early-outs are folded into the final test, which
 // is equivalent because tmin only grows and tmax only shrinks.  inv = 1/d is hoisted per ray
 // (same IEEE quotient the reference recomputes at every node).  Returns pierced; enter = final tmin.
@@ -113,7 +113,7 @@ __device__ __forceinline__ bool slab(const float4& mn, const float4& mx, const R
     return !(tmax <= tmin);
 }
 
-// ------------------------------------------------------------------ primitives
+// ------------------------------------------------------------------ primitives  [bucket:primitive_tests]
 // Sphere::hit (objects.rs:23-50), t only; point/normal are rebuilt for the winner in finish_hit
 __device__ __forceinline__ bool sphere_t(const float4& s, const Ray& r, float tmin, float tmax, float& t) {
     v3 oc = r.o - xyz(s);
@@ -169,7 +169,7 @@ __device__ __forceinline__ void offer(const SceneView& sc, LiteHit& best, float 
     if (take) { best.t = t; best.ref = ref; best.u = u; best.v = v; }
 }
 
-// t-culling threshold.  A subtree is skipped when its box entry lies beyond the current best by
+// t-culling threshold.  [bucket:stack_pop]  A subtree is skipped when its box entry lies beyond the current best by
 // more than this slack; the slack absorbs the few-ulp (sphere quadratic: worse) disagreement
 // between a primitive's computed t and its box's computed entry.  RTR_FLAG_EXHAUSTIVE disables
 // culling altogether (reference-shaped walk) and is used to validate the culled walk at scale.
@@ -182,7 +182,7 @@ struct StackEntry { uint32_t ref; float enter; };
 // Closest hit below `entry`; boxes are tested against (tmin, tmax), primitives as the reference does.  NESTED = a volume boundary / mesh sub-query:
 // volume leaves cannot occur there.  Volume leaves of the outer walk are handled by the caller
 // through `on_volume`.
-__device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+static __device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
                             float tmin, float tmax, const RngKey& key, StackEntry* stack, bool exhaustive,
                             Counters* cnt);
 
@@ -199,7 +199,7 @@ __device__ __forceinline__ uint32_t pop_next(const StackEntry* stack, int& sp, f
     return RTR_REF_DONE;
 }
 
-// Traversal is split into two resumable steps over the state (cur, sp, best):
+// Traversal is split into two resumable steps over the state (cur, sp, best):  [bucket:node_step]
 //   node_step  cur is an interior node: slab-test both children (one 64-B fetch), descend into the
 //              nearer pierced child, push the farther, or pop
 //   leaf_step  cur is a primitive: test it as the reference does, offer the hit, pop
@@ -234,6 +234,7 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
     }
 }
 
+// [bucket:leaf_step]
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, const RngKey& key, StackEntry* stack,
@@ -256,7 +257,7 @@ __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, in
     cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
 }
 
-// one "while-while" round: all lanes descend interior nodes together, then test their pending leaf together
+// one "while-while" round: all lanes descend interior nodes together, then test their pending leaf together  [bucket:nested_walk]
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk_round(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                            const RayInv& inv, float tmin, float tmax, const RngKey& key,
@@ -291,7 +292,7 @@ __device__ __forceinline__ bool boundary_t(const SceneView& sc, uint32_t entry, 
 }
 
 // Volume::hit (volume.rs:35-72).  Returns t, or NaN for None.
-__device__ __noinline__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+static __device__ __noinline__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
                                          float tmin, float tmax, const RngKey& key, StackEntry* stack,
                                          bool exhaustive, Counters* cnt) {
     const float NONE = __int_as_float(0x7fc00000);
@@ -346,7 +347,7 @@ __device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, cons
     return best;
 }
 
-// ------------------------------------------------------------------ HitRecord for the winner
+// ------------------------------------------------------------------ HitRecord for the winner  [bucket:finish_hit]
 struct Hit {
     v3 point, normal;
     float t;
@@ -389,7 +390,7 @@ __device__ __forceinline__ Hit finish_hit(const SceneView& sc, const Ray& r, con
     return h;
 }
 
-// ------------------------------------------------------------------ materials
+// ------------------------------------------------------------------ materials  [bucket:scatter]
 __device__ __forceinline__ bool near_zero(v3 v) {  // math.rs:6-9
     const float EPS = 1.0e-8f;
     return fabsf(v.x) < EPS && fabsf(v.y) < EPS && fabsf(v.z) < EPS;
@@ -482,7 +483,7 @@ __device__ __forceinline__ Scatter scatter_event(const SceneView& sc, bool clay,
     return s;
 }
 
-// ------------------------------------------------------------------ backgrounds (backgrounds.rs)
+// ------------------------------------------------------------------ backgrounds (backgrounds.rs)  [bucket:background]
 // Rust `f32 as usize` saturates (NaN -> 0); __float2ull_rz saturates the same way, NaN -> 0x8000...
 __device__ __forceinline__ unsigned long long f32_as_usize(float v) {
     return (v == v) ? __float2ull_rz(v) : 0ull;
@@ -508,7 +509,7 @@ __device__ __forceinline__ v3 background_sample(const SceneView& sc, const Ray& 
     return mk(texel.x, texel.y, texel.z);
 }
 
-// ------------------------------------------------------------------ camera (camera.rs:19-24)
+// ------------------------------------------------------------------ camera (camera.rs:19-24)  [bucket:camera]
 __device__ __forceinline__ Ray camera_sample_ray(const CameraBasis& cam, uint32_t W, uint32_t H, uint32_t x,
                                                  uint32_t y, const RngKey& key) {
     const uint4 j = draw(key, P_JITTER, 0);

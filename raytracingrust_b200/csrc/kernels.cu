@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_
         LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
 
         for (;;) {
-            // ---- lanes without a walk in flight: shade what they found, start their next ray
+            // ---- lanes without a walk in flight: shade what they found, start their next ray  [bucket:path_fsm]
             while (state != ST_DEAD && !walking) {
                 v3 L = mk(0.0f, 0.0f, 0.0f);
                 bool finished = false;  // this sample's radiance L is final
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_
             const uint32_t alive = __ballot_sync(FULL, state != ST_DEAD);
             if (!BVH || alive == 0u) break;
             const uint32_t keep = min(a.refill_threshold, (uint32_t)__popc(alive));
-            // ---- walk until enough lanes have finished to make a refill worth its divergence.  Each turn
+            // ---- walk until enough lanes have finished to make a refill worth its divergence.  Each turn  [bucket:schedule]
             // runs whichever step has more lanes waiting (majority rule): node steps while at least as
             // many lanes sit at interior nodes as at primitives, then one primitive step for the rest.
             do {
@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_
             } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
             walking = cur != RTR_REF_DONE;
         }
+        // [bucket:other]
         if (valid) {
             const float n = s_first < s_end ? (float)(s_end - s_first) : 0.0f;
             float4* dst = a.n_chunks == 1 ? a.accum : a.partials + (size_t)chunk * a.width * a.height;

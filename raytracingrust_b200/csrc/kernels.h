@@ -62,6 +62,9 @@ cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, u
 // Path state lives in HBM as SoA float4 streams, double-buffered so that wf_shade writes the
 // surviving paths DENSELY (warp ballot + popc + one atomic per warp) into the other buffer.
 #define RTR_WF_THREADS 128
+#ifndef RTR_WF_EXTEND_MIN_BLOCKS
+#define RTR_WF_EXTEND_MIN_BLOCKS 4
+#endif
 #define RTR_WF_MAX_DEPTH 256      // max_ray_depth is a u8 in the reference
 enum { WFC_WAVE = 0, WFC_QCOUNT = 8, WFC_FETCH = WFC_QCOUNT + RTR_WF_MAX_DEPTH + 8, WFC_WORDS = WFC_FETCH + RTR_WF_MAX_DEPTH + 8 };
 

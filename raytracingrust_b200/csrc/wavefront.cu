@@ -1,0 +1,326 @@
+// wavefront.cu — the wavefront variant of render() (lib/core/render.rs:61-127) for sm_100a.
+//
+// One WAVE traces `wave_samples` consecutive samples of every pixel to completion:
+//
+//   wf_generate   per-pixel sample generation (render.rs:88-92): camera rays -> path stream, bounce 0
+//   wf_extend     world.hit(ray, 1e-5, +INF) (render.rs:38) for every live path.  Persistent warps pull
+//                 rays from the stream with one atomic per refill; a lane whose walk has finished stores
+//                 its hit and takes the next ray while its neighbours keep walking, so the node/leaf
+//                 steps run with most lanes busy (the megakernel can only refill by running the whole
+//                 shading routine divergently).
+//   wf_shade      background / HitRecord / Material::scatter for every live path (render.rs:39-57),
+//                 then COMPACT: surviving paths are written densely into the other path buffer
+//                 (warp ballot + popc prefix + one atomicAdd per warp); finished paths add their clamped
+//                 radiance to the pixel (render.rs:95-99).
+//   wf_sum_samples / wf_next_wave   ordered per-pixel sum of the wave's samples, counters for the next wave
+//
+// All queue sizes live on the device (counters[]), so a wave is a fixed launch sequence with no host
+// synchronisation; capi.cpp captures it once into a CUDA graph and replays it per wave.
+// Results are bit-identical to the megakernel: the same per-path arithmetic and Philox counters, and each
+// pixel's samples are summed in sample order.
+#include "device_core.cuh"
+#include "kernels.h"
+
+namespace rtr {
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+struct WaveInfo { uint32_t begin, samples, n_paths; };
+__device__ __forceinline__ WaveInfo wave_info(const WfArgs& a) {
+    WaveInfo w;
+    const uint32_t wave = a.counters[WFC_WAVE];
+    w.begin = a.sample_begin + wave * a.wave_samples;
+    const uint32_t left = a.sample_end > w.begin ? a.sample_end - w.begin : 0u;
+    w.samples = min(a.wave_samples, left);
+    w.n_paths = w.samples * a.n_pixels;
+    return w;
+}
+
+// clamp + accumulate one finished sample (render.rs:95-99)
+__device__ __forceinline__ void finish_sample(const WfArgs& a, uint32_t pixel, uint32_t rel, v3 L) {
+    L.x = f32_clamp(L.x, 0.0f, a.clamp_indirect);
+    L.y = f32_clamp(L.y, 0.0f, a.clamp_indirect);
+    L.z = f32_clamp(L.z, 0.0f, a.clamp_indirect);
+    if (a.lbuf) {
+        a.lbuf[(size_t)rel * a.n_pixels + pixel] = make_float4(L.x, L.y, L.z, 1.0f);
+    } else {  // one path per pixel per wave: this thread is the only writer of the pixel in this launch
+        float4 c = a.accum[pixel];
+        c.x = c.x + L.x; c.y = c.y + L.y; c.z = c.z + L.z; c.w = c.w + 1.0f;
+        a.accum[pixel] = c;
+    }
+}
+
+__global__ void wf_begin_kernel(const WfArgs a) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < a.n_pixels) a.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (i < WFC_WORDS) a.counters[i] = 0u;
+}
+
+// ------------------------------------------------------------------ generate
+// Slots are handed out in 8x4-pixel tile order so that a warp of wf_extend starts with coherent rays.
+__global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArgs a) {
+    const WaveInfo w = wave_info(a);
+    const uint32_t tiles_x = (a.width + 7u) / 8u, tiles_y = (a.height + 3u) / 4u;
+    const uint32_t per_sample = tiles_x * tiles_y * 32u;
+    const uint64_t total = (uint64_t)per_sample * w.samples;
+    const uint32_t lane = threadIdx.x & 31u;
+    for (uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < total;
+         base += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = base + lane;
+        const uint32_t rel = (uint32_t)(i / per_sample), p = (uint32_t)(i - (uint64_t)rel * per_sample);
+        const uint32_t tile = p >> 5, tx = tile % tiles_x, ty = tile / tiles_x;
+        const uint32_t x = tx * 8u + (lane & 7u), y = ty * 4u + (lane >> 3);
+        const bool valid = i < total && x < a.width && y < a.height;
+        const uint32_t pixel = y * a.width + x;
+        if (valid && a.max_ray_depth == 0u) finish_sample(a, pixel, rel, mk(1.0f, 1.0f, 1.0f) * mk(0.0f, 0.0f, 0.0f));  // render.rs:34-36
+        const bool live = valid && a.max_ray_depth != 0u;
+        const uint32_t m = __ballot_sync(0xffffffffu, live);
+        if (m == 0u) continue;
+        uint32_t slot = 0;
+        if (lane == (uint32_t)(__ffs(m) - 1)) slot = atomicAdd(&a.counters[WFC_QCOUNT], (uint32_t)__popc(m));
+        slot = __shfl_sync(0xffffffffu, slot, __ffs(m) - 1) + __popc(m & lanemask_lt());
+        if (live) {
+            RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = pixel; key.sample = w.begin + rel; key.bounce = 0;
+            const Ray r = camera_sample_ray(a.cam, a.width, a.height, x, y, key);  // render.rs:88-92
+            a.in.o[slot] = make_float4(r.o.x, r.o.y, r.o.z, __uint_as_float(pixel));
+            a.in.d[slot] = make_float4(r.d.x, r.d.y, r.d.z, __uint_as_float(rel << 8));
+            a.in.thr[slot] = make_float4(1.0f, 1.0f, 1.0f, 0.0f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ extend
+template <bool EXHAUSTIVE, bool COUNT>
+__global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_extend_kernel(const WfArgs a) {
+    StackEntry stack[RTR_STACK_CAP];
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = a.counters[WFC_QCOUNT + a.bounce];
+    const WaveInfo w = wave_info(a);
+    uint32_t* fetch = &a.counters[WFC_FETCH + a.bounce];
+    Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
+
+    if (a.enable_bvh_tree == 0u) {  // Hittable for Scene: linear scan (scene.rs:141-156), uniform work per ray
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+            const float4 o = a.in.o[i], d = a.in.d[i];
+            Ray r; r.o = xyz(o); r.d = xyz(d);
+            RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = __float_as_uint(o.w);
+            key.sample = w.begin + (__float_as_uint(d.w) >> 8); key.bounce = __float_as_uint(d.w) & 0xFFu;
+            const LiteHit h = world_hit<EXHAUSTIVE, COUNT>(a.sc, false, r, 0.00001f, key, stack, &cnt);
+            a.hit[i] = make_float4(h.t, __uint_as_float(h.ref), h.u, h.v);
+        }
+    } else {
+        bool has = false, drained = false;
+        uint32_t idx = 0, cur = RTR_REF_DONE;
+        int sp = 0;
+        Ray r; r.o = r.d = mk(0.0f, 0.0f, 0.0f);
+        RayInv inv; inv.ix = inv.iy = inv.iz = 0.0f;
+        RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = key.sample = key.bounce = 0;
+        LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+        for (;;) {
+            // ---- refill idle lanes from the stream: one atomic per warp  [bucket:wf_fetch]
+            const uint32_t idle = __ballot_sync(FULL, !has);
+            if (!drained && idle != 0u) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(fetch, (uint32_t)__popc(idle));
+                base = __shfl_sync(FULL, base, 0);
+                if (!has) {
+                    idx = base + __popc(idle & lanemask_lt());
+                    if (idx < n) {
+                        const float4 o = a.in.o[idx], d = a.in.d[idx];
+                        r.o = xyz(o); r.d = xyz(d);
+                        key.pixel = __float_as_uint(o.w);
+                        key.sample = w.begin + (__float_as_uint(d.w) >> 8);
+                        key.bounce = __float_as_uint(d.w) & 0xFFu;
+                        inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z;
+                        best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+                        cur = walk_entry(a.sc.root_entry);
+                        sp = 0;
+                        has = true;
+                    }
+                }
+                drained = base + (uint32_t)__popc(idle) >= n;
+            }
+            const uint32_t busy = __ballot_sync(FULL, has);
+            if (busy == 0u) break;
+            const uint32_t keep = drained ? 1u : min(a.refill_threshold, (uint32_t)__popc(busy));
+            // ---- majority-rule step scheduling, as in the megakernel  [bucket:schedule]
+            do {
+                for (;;) {
+                    const bool at_node = RTR_REF_KIND(cur) == REF_NODE;
+                    const uint32_t mn = __ballot_sync(FULL, at_node);
+                    const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
+                    if (mn == 0u || __popc(mn) < __popc(ml)) break;
+                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, stack, &cnt);
+                }
+                if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
+                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, r, inv, 0.00001f, key, stack, &cnt);
+            } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
+            // [bucket:wf_store]
+            if (has && cur == RTR_REF_DONE) {
+                a.hit[idx] = make_float4(best.t, __uint_as_float(best.ref), best.u, best.v);
+                has = false;
+            }
+        }
+    }
+    if (COUNT) {
+        unsigned long long n_nodes = cnt.nodes, n_tris = cnt.tris, n_spheres = cnt.spheres;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            n_nodes += __shfl_xor_sync(FULL, n_nodes, o);
+            n_tris += __shfl_xor_sync(FULL, n_tris, o);
+            n_spheres += __shfl_xor_sync(FULL, n_spheres, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&a.stats[STAT_NODES], n_nodes);
+            atomicAdd(&a.stats[STAT_TRIS], n_tris);
+            atomicAdd(&a.stats[STAT_SPHERES], n_spheres);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ shade + compact
+template <bool COUNT>
+__global__ void __launch_bounds__(RTR_WF_THREADS) wf_shade_kernel(const WfArgs a) {
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = a.counters[WFC_QCOUNT + a.bounce];
+    const WaveInfo w = wave_info(a);
+    uint32_t* n_out = &a.counters[WFC_QCOUNT + a.bounce + 1];
+    Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
+    for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n; base += gridDim.x * blockDim.x) {
+        const uint32_t i = base + lane;
+        bool cont = false;
+        Ray ray; ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
+        v3 T = mk(0.0f, 0.0f, 0.0f);
+        uint32_t pixel = 0, rel = 0, depth = 0;
+        if (i < n) {
+            const float4 o = a.in.o[i], d = a.in.d[i], t = a.in.thr[i], h = a.hit[i];
+            ray.o = xyz(o); ray.d = xyz(d);
+            T = xyz(t);
+            pixel = __float_as_uint(o.w);
+            rel = __float_as_uint(d.w) >> 8;
+            depth = __float_as_uint(d.w) & 0xFFu;
+            RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = pixel; key.sample = w.begin + rel; key.bounce = depth;
+            LiteHit lh; lh.t = h.x; lh.ref = __float_as_uint(h.y); lh.u = h.z; lh.v = h.w;
+            v3 L = mk(0.0f, 0.0f, 0.0f);
+            if (lh.ref == REF_EMPTY_VALUE) {
+                L = T * background_sample(a.sc, ray, COUNT ? &cnt : nullptr);  // render.rs:57
+            } else {
+                const Hit hit = finish_hit(a.sc, ray, lh);
+                if (a.mode == RTR_MODE_FULL || a.mode == RTR_MODE_CLAY) {
+                    const Scatter sc = scatter_event(a.sc, a.mode == RTR_MODE_CLAY, hit.material, ray, hit, key);  // :40-41
+                    if (sc.some) {  // attenuation * trace_ray(scattered, depth + 1)  (:51-52)
+                        T = T * sc.attenuation;
+                        ray = sc.ray;
+                        ++depth;
+                        if (depth >= a.max_ray_depth) L = T * mk(0.0f, 0.0f, 0.0f);  // :34-36
+                        else cont = true;
+                    } else {
+                        L = T * sc.attenuation;  // :54
+                    }
+                } else if (a.mode == RTR_MODE_NORMAL) {  // :42-45
+                    L = T * (0.5f * (normalize(hit.normal) + mk(1.0f, 1.0f, 1.0f)));
+                } else {
+                    L = T * mk(0.0f, 0.0f, 0.0f);  // Random (:46-48)
+                }
+            }
+            if (!cont) finish_sample(a, pixel, rel, L);
+        }
+        // ---- compaction: survivors go densely into the other buffer  [bucket:wf_compact]
+        const uint32_t m = __ballot_sync(FULL, cont);
+        if (m != 0u) {
+            const int leader = __ffs(m) - 1;
+            uint32_t slot = 0;
+            if ((int)lane == leader) slot = atomicAdd(n_out, (uint32_t)__popc(m));
+            slot = __shfl_sync(FULL, slot, leader) + __popc(m & lanemask_lt());
+            if (cont) {
+                a.out.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(pixel));
+                a.out.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float((rel << 8) | depth));
+                a.out.thr[slot] = make_float4(T.x, T.y, T.z, 0.0f);
+            }
+        }
+    }
+    if (COUNT) {
+        unsigned long long n_env = cnt.env;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) n_env += __shfl_xor_sync(FULL, n_env, o);
+        if (lane == 0 && n_env) atomicAdd(&a.stats[STAT_ENV], n_env);
+    }
+}
+
+// ------------------------------------------------------------------ end of wave
+// accum[p] += lbuf[0][p] + lbuf[1][p] + ... one sample at a time, i.e. the reference's sequential sum (render.rs:99)
+__global__ void wf_sum_samples_kernel(const WfArgs a) {
+    const WaveInfo w = wave_info(a);
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < a.n_pixels; p += gridDim.x * blockDim.x) {
+        float4 c = a.accum[p];
+        for (uint32_t rel = 0; rel < w.samples; ++rel) {
+            const float4 l = a.lbuf[(size_t)rel * a.n_pixels + p];
+            c.x = c.x + l.x; c.y = c.y + l.y; c.z = c.z + l.z; c.w = c.w + l.w;
+        }
+        a.accum[p] = c;
+    }
+}
+
+// one block: count the wave's rays (every queued path-bounce is one world.hit query), reset the queues, next wave
+__global__ void wf_next_wave_kernel(const WfArgs a) {
+    unsigned long long rays = 0;
+    for (uint32_t b = threadIdx.x; b < RTR_WF_MAX_DEPTH; b += blockDim.x)
+        if (b < a.max_ray_depth) rays += a.counters[WFC_QCOUNT + b];
+    if (rays) atomicAdd(&a.stats[STAT_RAYS], rays);
+    __syncthreads();
+    for (uint32_t i = WFC_QCOUNT + threadIdx.x; i < WFC_WORDS; i += blockDim.x) a.counters[i] = 0u;
+    if (threadIdx.x == 0) a.counters[WFC_WAVE] += 1u;
+}
+
+// ------------------------------------------------------------------ launchers
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count) {
+    int n = 0;
+    cudaError_t e;
+    if (exhaustive) e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<true, true>, RTR_WF_THREADS, 0)
+                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<true, false>, RTR_WF_THREADS, 0);
+    else e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<false, true>, RTR_WF_THREADS, 0)
+                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<false, false>, RTR_WF_THREADS, 0);
+    return e == cudaSuccess ? n : 0;
+}
+
+cudaError_t launch_wf_begin(const WfArgs& a, cudaStream_t st) {
+    const uint32_t n = a.n_pixels > (uint32_t)WFC_WORDS ? a.n_pixels : (uint32_t)WFC_WORDS;
+    wf_begin_kernel<<<(n + 255) / 256, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st) {
+    wf_generate_kernel<<<grid, RTR_WF_THREADS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st) {
+    if (exhaustive) {
+        if (count) wf_extend_kernel<true, true><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+        else wf_extend_kernel<true, false><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+    } else {
+        if (count) wf_extend_kernel<false, true><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+        else wf_extend_kernel<false, false><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_shade(const WfArgs& a, int grid, bool count, cudaStream_t st) {
+    if (count) wf_shade_kernel<true><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+    else wf_shade_kernel<false><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_end_wave(const WfArgs& a, int grid, cudaStream_t st) {
+    if (a.lbuf) wf_sum_samples_kernel<<<grid, 256, 0, st>>>(a);
+    wf_next_wave_kernel<<<1, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace rtr
