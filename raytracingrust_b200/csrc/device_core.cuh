@@ -40,11 +40,24 @@ __device__ __forceinline__ v3 xyz(const float4& q) { return mk(q.x, q.y, q.z); }
 struct Ray { v3 o, d; };
 __device__ __forceinline__ v3 ray_at(const Ray& r, float t) { return r.o + r.d * t; }  // ray.rs:15-17
 
-// Plain (non-__ldg) 128-bit loads: with ld.global.nc nvcc 12.9 was observed to hoist a leaf load above
-// the ref-kind test that guards it (reading spheres[node index], out of bounds) — a plain load may not
-// be speculated.  L1 caches global loads on sm_100 either way.
-__device__ __forceinline__ float4 ldg4(const F4* p) { return *reinterpret_cast<const float4*>(p); }
-__device__ __forceinline__ uint4 ldgu4(const U4* p) { return *reinterpret_cast<const uint4*>(p); }
+// 128-bit global loads, one LDG.E.128 each.  Written as volatile inline PTX for two reasons seen in the SASS:
+//  * through a by-value struct the compiler treats scene pointers as GENERIC and, worse, splits a float4
+//    load whose components are used under different conditions into up to four narrower LD.E (10 load
+//    instructions per 64-B node instead of 4) — and the kernels are bound by L1 wavefronts (ncu:
+//    l1tex__data_pipe_lsu_wavefronts 73 % of peak), where every extra divergent load instruction costs
+//    one wavefront per distinct cache line;
+//  * with ld.global.nc (__ldg) nvcc 12.9 hoisted a leaf load above the ref-kind test that guards it
+//    (reading spheres[node index], out of bounds); a volatile asm is never speculated.
+__device__ __forceinline__ float4 ldg4(const F4* p) {
+    float4 v;
+    asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint4 ldgu4(const U4* p) {
+    uint4 v;
+    asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 
 // ------------------------------------------------------------------ Philox4x32-10, keyed draws  [bucket:rng]
 __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
@@ -92,23 +105,25 @@ struct Counters { uint32_t nodes, tris, spheres, env; };
 
 // ------------------------------------------------------------------ AABB::hit (aabb.rs:81-137)  [bucket:slab]
 // Same t0/t1/swap/update sequence; the per-axis early-outs are folded into the final test, which
-// is equivalent because tmin only grows and tmax only shrinks.  inv = 1/d is hoisted per ray
+// is equivalent because tmin only grows and tmax only shrinks.  `if (t0 > tmin) tmin = t0` is written
+// fmaxf(tmin, t0): identical for every input (a NaN t0 — 0 * inf — leaves tmin unchanged in both forms;
+// tmin/tmax themselves are never NaN) and one FMNMX instead of FSETP + FSEL.  inv = 1/d is hoisted per ray
 // (same IEEE quotient the reference recomputes at every node).  Returns pierced; enter = final tmin.
 struct RayInv { float ix, iy, iz; };
 __device__ __forceinline__ bool slab(const float4& mn, const float4& mx, const Ray& r, const RayInv& inv,
                                      float tmin, float tmax, float& enter) {
     float t0 = (mn.x - r.o.x) * inv.ix, t1 = (mx.x - r.o.x) * inv.ix;
     if (inv.ix < 0.0f) { float s = t0; t0 = t1; t1 = s; }
-    if (t0 > tmin) tmin = t0;
-    if (t1 < tmax) tmax = t1;
+    tmin = fmaxf(tmin, t0);
+    tmax = fminf(tmax, t1);
     t0 = (mn.y - r.o.y) * inv.iy; t1 = (mx.y - r.o.y) * inv.iy;
     if (inv.iy < 0.0f) { float s = t0; t0 = t1; t1 = s; }
-    if (t0 > tmin) tmin = t0;
-    if (t1 < tmax) tmax = t1;
+    tmin = fmaxf(tmin, t0);
+    tmax = fminf(tmax, t1);
     t0 = (mn.z - r.o.z) * inv.iz; t1 = (mx.z - r.o.z) * inv.iz;
     if (inv.iz < 0.0f) { float s = t0; t0 = t1; t1 = s; }
-    if (t0 > tmin) tmin = t0;
-    if (t1 < tmax) tmax = t1;
+    tmin = fmaxf(tmin, t0);
+    tmax = fminf(tmax, t1);
     enter = tmin;
     return !(tmax <= tmin);
 }

@@ -13,7 +13,7 @@ namespace rtr {
 
 #define RTR_MEGA_THREADS 128
 #ifndef RTR_MEGA_MIN_BLOCKS
-#define RTR_MEGA_MIN_BLOCKS 4  // resident CTAs per SM the register allocation must allow
+#define RTR_MEGA_MIN_BLOCKS 7  // resident CTAs per SM the register allocation must allow (swept on B200: 4..8)
 #endif
 
 struct v3 { float x, y, z; };
@@ -63,7 +63,7 @@ cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, u
 // surviving paths DENSELY (warp ballot + popc + one atomic per warp) into the other buffer.
 #define RTR_WF_THREADS 128
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS
-#define RTR_WF_EXTEND_MIN_BLOCKS 4
+#define RTR_WF_EXTEND_MIN_BLOCKS 8
 #endif
 #define RTR_WF_MAX_DEPTH 256      // max_ray_depth is a u8 in the reference
 enum { WFC_WAVE = 0, WFC_QCOUNT = 8, WFC_FETCH = WFC_QCOUNT + RTR_WF_MAX_DEPTH + 8, WFC_WORDS = WFC_FETCH + RTR_WF_MAX_DEPTH + 8 };

@@ -34,8 +34,8 @@ def test_wavefront_matches_oracle_same_stream(ctx, name):
         assert st_d["rays"] == st_o["rays"]
 
 
-@pytest.mark.parametrize("name,W,H,spp", [("simple", 800, 600, 3), ("mesh_hdri", 800, 600, 2), ("volumes", 800, 600, 2),
-                                          ("benchmark", 800, 600, 5)])
+@pytest.mark.parametrize("name,W,H,spp", [("simple", 1024, 768, 3), ("mesh_hdri", 1024, 768, 2), ("volumes", 1024, 768, 2),
+                                          ("benchmark", 1024, 768, 5)])
 def test_wavefront_bit_identical_to_megakernel(ctx, name, W, H, spp):
     scene = _scenes.mesh_hdri(256, 128) if name == "mesh_hdri" else _scenes.volumes(128, 64) if name == "volumes" \
         else getattr(_scenes, name)()
