@@ -236,7 +236,6 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     step(upload(s, flat.sphere_info, &v.sphere_info, ctx->stream));
     step(upload(s, flat.tris, &v.tris, ctx->stream));
     step(upload(s, flat.tri_vn, &v.tri_vn, ctx->stream));
-    step(upload(s, flat.tri_info, &v.tri_info, ctx->stream));
     step(upload(s, flat.volumes, &v.volumes, ctx->stream));
     step(upload(s, flat.objects, &v.objects, ctx->stream));
     step(upload(s, flat.materials, &v.materials, ctx->stream));

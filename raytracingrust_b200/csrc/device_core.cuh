@@ -53,6 +53,12 @@ __device__ __forceinline__ float4 ldg4(const F4* p) {
     asm volatile("ld.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
     return v;
 }
+// 256-bit global load (LDG.E.ENL2.256, new with sm_100): one instruction fetches half a 64-B node / triangle
+// record, halving the L1 wavefronts of a divergent fetch again.  p must be 32-byte aligned.
+__device__ __forceinline__ void ldg8(const F4* p, float4& a, float4& b) {
+    asm volatile("ld.global.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
 __device__ __forceinline__ uint4 ldgu4(const U4* p) {
     uint4 v;
     asm volatile("ld.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
@@ -175,7 +181,7 @@ struct LiteHit {
 __device__ __forceinline__ uint32_t leaf_rank(const SceneView& sc, uint32_t ref) {
     uint32_t k = RTR_REF_KIND(ref), i = RTR_REF_INDEX(ref);
     if (k == REF_SPHERE) return sc.sphere_info[i].w;
-    if (k == REF_TRI) return sc.tri_info[i].w;
+    if (k == REF_TRI) return __float_as_uint(sc.tris[(size_t)i * 4 + 3].w);
     return sc.volumes[i].rank;
 }
 __device__ __forceinline__ void offer(const SceneView& sc, LiteHit& best, float t, uint32_t ref, float u, float v) {
@@ -221,11 +227,15 @@ __device__ __forceinline__ uint32_t pop_next(const StackEntry* stack, int& sp, f
 // cur == RTR_REF_DONE: finished.  Callers schedule the steps: walk() (nested queries, batch kernel)
 // runs the classic "while-while" order; the render kernels pick, per warp, whichever step has more
 // lanes waiting and refill finished lanes in between (kernels.cu, wavefront.cu).
-template <bool EXHAUSTIVE, bool COUNT>
+// WIDE: fetch with 256-bit loads.  Off inside volume_hit's nested walks: ptxas 12.9 segfaults when a
+// non-inlined device function containing ld.global.v8 is called from two kernels of one module.
+template <bool EXHAUSTIVE, bool COUNT, bool WIDE = true>
 __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, float tmax, StackEntry* stack, Counters* cnt) {
     const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
-    const float4 q0 = ldg4(q), q1 = ldg4(q + 1), q2 = ldg4(q + 2), q3 = ldg4(q + 3);
+    float4 q0, q1, q2, q3;
+    if (WIDE) { ldg8(q, q0, q1); ldg8(q + 2, q2, q3); }
+    else { q0 = ldg4(q); q1 = ldg4(q + 1); q2 = ldg4(q + 2); q3 = ldg4(q + 3); }
     uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
     float le = -RTR_INF, re = -RTR_INF;
     bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
@@ -256,10 +266,13 @@ __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, in
                                           Counters* cnt) {
     const uint32_t kind = RTR_REF_KIND(cur);
     if (kind == REF_TRI) {
-        const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 3;
+        const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 4;
+        float4 q0, q1;
+        if (!NESTED) ldg8(q, q0, q1);
+        else { q0 = ldg4(q); q1 = ldg4(q + 1); }
         float t, u, v;
         if (COUNT) cnt->tris++;
-        if (triangle_t(ldg4(q), ldg4(q + 1), ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
+        if (triangle_t(q0, q1, ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
     } else if (kind == REF_SPHERE) {
         float t;
         if (COUNT) cnt->spheres++;
@@ -277,7 +290,7 @@ template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk_round(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                            const RayInv& inv, float tmin, float tmax, const RngKey& key,
                                            StackEntry* stack, Counters* cnt) {
-    while (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(sc, cur, sp, best, r, inv, tmin, tmax, stack, cnt);
+    while (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT, !NESTED>(sc, cur, sp, best, r, inv, tmin, tmax, stack, cnt);
     if (cur == RTR_REF_DONE) return;
     leaf_step<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
 }
@@ -384,11 +397,11 @@ __device__ __forceinline__ Hit finish_hit(const SceneView& sc, const Ray& r, con
         n = (h.point - xyz(s)) / s.w;
         h.object = info.x; h.primitive = 0; h.material = info.z;
     } else if (kind == REF_TRI) {
-        const F4* q = sc.tris + (size_t)i * 3;
+        const F4* q = sc.tris + (size_t)i * 4;
         const F4* vn = sc.tri_vn + (size_t)i * 3;
         const v3 fn = mk(q[0].w, q[1].w, q[2].w);
         const v3 n0 = xyz(ldg4(vn)), n1 = xyz(ldg4(vn + 1)), n2 = xyz(ldg4(vn + 2));
-        const uint4 info = ldgu4(sc.tri_info + i);
+        const uint4 info = ldgu4(reinterpret_cast<const U4*>(q + 3));
         n = lh.u * n1 + lh.v * n2 + (1.0f - lh.u - lh.v) * n0;  // mesh.rs:185
         // `normal.angle(face).0 > 0` (mesh.rs:187) with angle = atan2(|n x f|, n.f):
         // atan2(y>=0, x) > 0  <=>  y > 0 || (y == 0 && x negative (incl. -0)); NaN -> false

@@ -26,7 +26,7 @@ namespace rtr {
 enum : uint32_t {
     REF_NODE = 0u,    // index of a 64-B node
     REF_SPHERE = 1u,  // slot in spheres[] / sphere_info[]
-    REF_TRI = 2u,     // slot in tris[] (x3) / tri_vn[] (x3) / tri_info[]
+    REF_TRI = 2u,     // slot in tris[] (x4) / tri_vn[] (x3)
     REF_VOLUME = 3u,  // index in volumes[]
     REF_EMPTY = 7u    // BvhNode::None
 };
@@ -79,9 +79,9 @@ struct SceneView {
     const F4* nodes;          // 4 per node
     const F4* spheres;        // (cx, cy, cz, r) per slot
     const PrimInfo* sphere_info;
-    const F4* tris;           // 3 per slot: (v0.xyz, fn.x) (e1.xyz, fn.y) (e2.xyz, fn.z)
+    const F4* tris;           // 4 per slot (64 B, one aligned record = two 256-bit loads): (v0.xyz, fn.x) (e1.xyz, fn.y)
+                              // (e2.xyz, fn.z) bits(PrimInfo)
     const F4* tri_vn;         // 3 per slot: vertex normals n0, n1, n2 (w unused)
-    const PrimInfo* tri_info;
     const VolumeRec* volumes;
     const ObjectRec* objects;
     const MaterialRec* materials;

@@ -164,7 +164,13 @@ struct Flattener {
                 const float* nn = &m.normals[3 * (size_t)t[k]];
                 f.out.tri_vn.push_back(F4{nn[0], nn[1], nn[2], 0.0f});
             }
-            f.out.tri_info.push_back(PrimInfo{object, h, m.material, f.rank++});
+            {
+                const PrimInfo info{object, h, m.material, f.rank++};
+                F4 bits;
+                std::memcpy(&bits, &info, sizeof(bits));
+                f.out.tris.push_back(bits);
+                f.out.tri_info.push_back(info);
+            }
             return Built{RTR_MAKE_REF(REF_TRI, slot), Box{}, false, 1};
         }
     };
