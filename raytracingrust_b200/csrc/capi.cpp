@@ -410,7 +410,16 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
 // launches the render kernels for this call's sample slice into accum_dev; fills stats (async)
 static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
                               float4* accum_dev, bool timed, rtr_stats* stats_out) {
-    if (p->kernel == RTR_KERNEL_WAVEFRONT) return render_wavefront(ctx, scene, p, accum_dev, timed, stats_out);
+    // RTR_KERNEL_AUTO (measured on B200, DESIGN.md "Megakernel or wavefront"): a BVH walk whose length varies
+    // from ray to ray is where the wavefront's cheap lane refill pays for its path-state traffic; the linear
+    // scan (BVH off), tiny trees and renders too small to fill a wave stay in the single-launch megakernel.
+    uint32_t kernel = p->kernel;
+    if (kernel == RTR_KERNEL_AUTO) {
+        const uint64_t paths = (uint64_t)p->width * p->height * (p->sample_count ? p->sample_count : p->settings.samples_per_pixel);
+        const bool wf = p->settings.enable_bvh_tree != 0 && scene->n_nodes >= 64 && paths >= (1ull << 20);
+        kernel = wf ? RTR_KERNEL_WAVEFRONT : RTR_KERNEL_MEGAKERNEL;
+    }
+    if (kernel == RTR_KERNEL_WAVEFRONT) return render_wavefront(ctx, scene, p, accum_dev, timed, stats_out);
     const uint32_t W = p->width, H = p->height;
     const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
     const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;

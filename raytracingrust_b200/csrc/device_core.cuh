@@ -200,6 +200,33 @@ __device__ __forceinline__ float cull_limit(float best_t) {
 
 struct StackEntry { uint32_t ref; float enter; };
 
+// Traversal stacks.  LocalStack: per-thread array in local memory.  ShortStack: the first SHORT entries of every
+// thread live in shared memory, laid out [entry][thread] so a warp's access is conflict-free and costs two
+// wavefronts whatever the lanes' depths are (in local memory lanes at different depths hit different lines:
+// ncu showed local traffic at 40 % of the L1 wavefronts of wf_extend); deeper entries spill to local memory.
+struct LocalStack {
+    StackEntry* p;
+    __device__ __forceinline__ void put(int sp, uint32_t ref, float enter) const { p[sp].ref = ref; p[sp].enter = enter; }
+    __device__ __forceinline__ StackEntry get(int sp) const { return p[sp]; }
+    __device__ __forceinline__ StackEntry* nested(int sp) const { return p + sp; }  // scratch for a nested query
+};
+template <int SHORT, int STRIDE>
+struct ShortStack {
+    uint2* sh;        // &smem[0][threadIdx.x]
+    StackEntry* loc;  // spill area
+    __device__ __forceinline__ void put(int sp, uint32_t ref, float enter) const {
+        if (sp < SHORT) sh[sp * STRIDE] = make_uint2(ref, __float_as_uint(enter));
+        else { loc[sp - SHORT].ref = ref; loc[sp - SHORT].enter = enter; }
+    }
+    __device__ __forceinline__ StackEntry get(int sp) const {
+        StackEntry e;
+        if (sp < SHORT) { const uint2 v = sh[sp * STRIDE]; e.ref = v.x; e.enter = __uint_as_float(v.y); }
+        else e = loc[sp - SHORT];
+        return e;
+    }
+    __device__ __forceinline__ StackEntry* nested(int sp) const { return loc + (sp > SHORT ? sp - SHORT : 0); }
+};
+
 // Closest hit below `entry`; boxes are tested against (tmin, tmax), primitives as the reference does.  NESTED = a volume boundary / mesh sub-query:
 // volume leaves cannot occur there.  Volume leaves of the outer walk are handled by the caller
 // through `on_volume`.
@@ -210,12 +237,13 @@ static __device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, co
 #define RTR_REF_DONE 0xDFFFFFFFu  // kind 6: traversal finished (never stored in a node)
 
 // pop the next stack entry that survives t-culling
-template <bool EXHAUSTIVE>
-__device__ __forceinline__ uint32_t pop_next(const StackEntry* stack, int& sp, float best_t) {
+template <bool EXHAUSTIVE, typename STACK>
+__device__ __forceinline__ uint32_t pop_next(const STACK& stack, int& sp, float best_t) {
     const float lim = cull_limit(best_t);
     while (sp > 0) {
         --sp;
-        if (EXHAUSTIVE || !(stack[sp].enter > lim)) return stack[sp].ref;
+        const StackEntry e = stack.get(sp);
+        if (EXHAUSTIVE || !(e.enter > lim)) return e.ref;
     }
     return RTR_REF_DONE;
 }
@@ -229,9 +257,9 @@ __device__ __forceinline__ uint32_t pop_next(const StackEntry* stack, int& sp, f
 // lanes waiting and refill finished lanes in between (kernels.cu, wavefront.cu).
 // WIDE: fetch with 256-bit loads.  Off inside volume_hit's nested walks: ptxas 12.9 segfaults when a
 // non-inlined device function containing ld.global.v8 is called from two kernels of one module.
-template <bool EXHAUSTIVE, bool COUNT, bool WIDE = true>
+template <bool EXHAUSTIVE, bool COUNT, bool WIDE = true, typename STACK>
 __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
-                                          const RayInv& inv, float tmin, float tmax, StackEntry* stack, Counters* cnt) {
+                                          const RayInv& inv, float tmin, float tmax, const STACK& stack, Counters* cnt) {
     const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
     float4 q0, q1, q2, q3;
     if (WIDE) { ldg8(q, q0, q1); ldg8(q + 2, q2, q3); }
@@ -248,7 +276,7 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
     }
     if (lh && rh) {
         if (re < le) { uint32_t tr = lref; lref = rref; rref = tr; float te = le; le = re; re = te; }
-        stack[sp].ref = rref; stack[sp].enter = re; ++sp;
+        stack.put(sp, rref, re); ++sp;
         cur = lref;
     } else if (lh) {
         cur = lref;
@@ -260,9 +288,9 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
 }
 
 // [bucket:leaf_step]
-template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED, typename STACK>
 __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
-                                          const RayInv& inv, float tmin, const RngKey& key, StackEntry* stack,
+                                          const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
                                           Counters* cnt) {
     const uint32_t kind = RTR_REF_KIND(cur);
     if (kind == REF_TRI) {
@@ -279,7 +307,7 @@ __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, in
         if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(cur)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
     } else if (!NESTED && kind == REF_VOLUME) {
         const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
-        float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack + sp, EXHAUSTIVE, COUNT ? cnt : nullptr);
+        float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack.nested(sp), EXHAUSTIVE, COUNT ? cnt : nullptr);
         if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
     }
     cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
@@ -289,7 +317,7 @@ __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, in
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk_round(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                            const RayInv& inv, float tmin, float tmax, const RngKey& key,
-                                           StackEntry* stack, Counters* cnt) {
+                                           const LocalStack& stack, Counters* cnt) {
     while (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT, !NESTED>(sc, cur, sp, best, r, inv, tmin, tmax, stack, cnt);
     if (cur == RTR_REF_DONE) return;
     leaf_step<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
@@ -303,7 +331,8 @@ __device__ __forceinline__ void walk(const SceneView& sc, uint32_t entry, const 
                                      Counters* cnt) {
     uint32_t cur = walk_entry(entry);
     int sp = 0;
-    while (cur != RTR_REF_DONE) walk_round<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, tmax, key, stack, cnt);
+    LocalStack ls; ls.p = stack;
+    while (cur != RTR_REF_DONE) walk_round<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, tmax, key, ls, cnt);
 }
 
 // boundary.hit(ray, tmin, +INF) of a volume boundary: only t is consumed (volume.rs:36-37)

@@ -24,7 +24,11 @@ enum { ST_FRESH = 0, ST_LAUNCH = 1, ST_SHADE = 2, ST_DEAD = 3 };
 
 template <bool EXHAUSTIVE, bool COUNT, bool BVH>
 __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_megakernel(const RenderArgs a) {
-    StackEntry stack[RTR_STACK_CAP];
+    StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
+    __shared__ uint2 short_stack[BVH ? RTR_SHORT_STACK : 1][RTR_MEGA_THREADS];
+    ShortStack<RTR_SHORT_STACK, RTR_MEGA_THREADS> wstack;
+    wstack.sh = &short_stack[0][threadIdx.x];
+    wstack.loc = stack;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t FULL = 0xffffffffu;
     unsigned long long n_rays = 0, n_nodes = 0, n_tris = 0, n_spheres = 0, n_env = 0;
@@ -134,10 +138,10 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_
                     const uint32_t mn = __ballot_sync(FULL, at_node);
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
-                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, ray, inv, 0.00001f, RTR_INF, stack, &cnt);
+                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, ray, inv, 0.00001f, RTR_INF, wstack, &cnt);
                 }
                 if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
-                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, ray, inv, 0.00001f, key, stack, &cnt);
+                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, ray, inv, 0.00001f, key, wstack, &cnt);
             } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
             walking = cur != RTR_REF_DONE;
         }

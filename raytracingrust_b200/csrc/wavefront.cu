@@ -96,7 +96,11 @@ __global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArg
 // ------------------------------------------------------------------ extend
 template <bool EXHAUSTIVE, bool COUNT>
 __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_extend_kernel(const WfArgs a) {
-    StackEntry stack[RTR_STACK_CAP];
+    StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
+    __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_THREADS];
+    ShortStack<RTR_SHORT_STACK, RTR_WF_THREADS> wstack;
+    wstack.sh = &short_stack[0][threadIdx.x];
+    wstack.loc = stack;
     const uint32_t FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = a.counters[WFC_QCOUNT + a.bounce];
@@ -155,10 +159,10 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_e
                     const uint32_t mn = __ballot_sync(FULL, at_node);
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
-                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, stack, &cnt);
+                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
                 }
                 if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
-                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, r, inv, 0.00001f, key, stack, &cnt);
+                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, r, inv, 0.00001f, key, wstack, &cnt);
             } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
             // [bucket:wf_store]
             if (has && cur == RTR_REF_DONE) {

@@ -104,3 +104,15 @@ def test_wavefront_zero_sized_and_empty(ctx):
     for W, H in ((0, 10), (10, 0)):
         rgba, acc, st = ds.render(wf(s, W, H))
         assert rgba.size == 0 and st["rays"] == 0
+
+
+def test_auto_kernel_choice(ctx):
+    """RTR_KERNEL_AUTO: wavefront for BVH walks big enough to fill a wave, megakernel otherwise (capi.cpp)."""
+    mesh = _scenes.mesh_hdri(64, 32)
+    mesh.settings.samples_per_pixel = 2
+    ds = ctx.upload(mesh)
+    assert ds.render(rt.make_params(mesh, 1024, 768, seed=1))[2]["kernel_used"] == A.KERNEL_WAVEFRONT
+    assert ds.render(rt.make_params(mesh, 64, 64, seed=1))[2]["kernel_used"] == A.KERNEL_MEGAKERNEL
+    flat = _scenes.benchmark()  # ships enable_bvh_tree = false
+    flat.settings.samples_per_pixel = 2
+    assert ctx.upload(flat).render(rt.make_params(flat, 1024, 768, seed=1))[2]["kernel_used"] == A.KERNEL_MEGAKERNEL
