@@ -36,7 +36,7 @@ struct rtr_context {
     uchar4* rgba = nullptr; size_t rgba_pixels = 0;
     float4* wf_state = nullptr; size_t wf_state_elems = 0;  // wavefront: 7 path streams (+ lbuf), see render_wavefront
     uint32_t* wf_counters = nullptr;
-    uint32_t wf_refill_threshold = 24;  // RTR_WF_REFILL_THRESHOLD
+    uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
     uint64_t wf_target_paths = 1ull << 23;  // RTR_WF_PATHS: paths in flight per wave
     int wf_use_graph = 1;  // RTR_WF_GRAPH
     char* batch_in = nullptr; size_t batch_in_bytes = 0;
