@@ -31,6 +31,7 @@ WORKLOADS = {
     "simple": ("simple", 1920, 1080, 1024, "scenes/simple.json 1920x1080x1024spp (102 spheres, BVH on)"),
     "mesh_hdri": ("mesh_hdri", 1920, 1080, 256, "house+plane+fancy_monkey meshes, synthetic 4096x2048 HDRI, 1920x1080x256spp"),
     "volumes": ("volumes", 1920, 1080, 64, "mesh/sphere-bounded media over plane, synthetic HDRI, 1920x1080x64spp"),
+    "bvh_stress": ("bvh_stress", 2048, 2048, 16, "C3(ii): 1M random spheres (seed 42), pinhole 2048x2048 from (0,0,120), Lambertian, depth 6, 16spp"),
 }
 
 
@@ -40,7 +41,16 @@ def make_scene(name):
         return _scenes.mesh_hdri(4096, 2048)
     if name == "volumes":
         return _scenes.volumes(2048, 1024)
+    if name == "bvh_stress":
+        return _scenes.random_spheres(1_000_000)
     return getattr(_scenes, name)()
+
+
+def algorithmic_ops(st):
+    """SURVEY §8(d) issue-slot roofline: FP32 work per unit with 1/d hoisted — slab test 21 ops, Moeller-Trumbore 51,
+    sphere 33, env lookup 40 (normalize + acos + atan2), and 150 per ray for the path bookkeeping + scatter
+    (~2 Philox4x32-10 draws)."""
+    return 21 * st["nodes_visited"] + 51 * st["tri_tests"] + 33 * st["sphere_tests"] + 40 * st["env_lookups"] + 150 * st["rays"]
 
 
 def algorithmic_bytes(st):
@@ -93,7 +103,9 @@ def cpu_render(scene, W, H, spp_sample, seed=0, count_work=False):
     from oracle import orc
     o = orc.OracleScene(scene)
     p = rt.make_params(scene, W, H, seed=seed, sample_count=spp_sample)
-    _, _, st = o.render(p, threads=0, count_work=count_work, want_rgba=True, want_accum=False)
+    # all host cores this process may run on (torchrun exports OMP_NUM_THREADS=1, so do not rely on the OpenMP default)
+    threads = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    _, _, st = o.render(p, threads=threads, count_work=count_work, want_rgba=True, want_accum=False)
     return st
 
 
@@ -132,7 +144,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="benchmark", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug only)")
-    ap.add_argument("--cpu-spp", type=int, default=4, help="spp of the bounded CPU sample")
+    ap.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--kernel", type=int, default=0)
     args = ap.parse_args()
@@ -177,7 +189,7 @@ def main():
 
     # rays per step and work counters (untimed, counting variant of the kernel)
     pc = rt.make_params(scene, W, H, seed=0, sample_begin=rank * spp, sample_count=spp, kernel=args.kernel,
-                        flags=A.FLAG_COUNT_WORK)
+                        flags=A.FLAG_COUNT_WORK | A.FLAG_REFERENCE_TREE)  # algorithmic work is DEFINED on the reference topology
     st_count = dev_scene.render_accumulate_device(pc, accum.data_ptr(), want_stats=True)
     for _ in range(args.warmup):
         step()
@@ -238,6 +250,7 @@ def main():
             pass
         peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
         k_ms = float(np.mean(kern_ms))
+        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
         alg = algorithmic_bytes(st_count)
         achieved = alg / (k_ms * 1e-3) / 1e9
         traffic = None
@@ -264,7 +277,14 @@ def main():
                          "traffic": traffic, "peak_source": peak_src, "kernel": "render_megakernel" if st_count["kernel_used"] == 1 else "wavefront wave sequence (wf_extend dominant)",
                          "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                          "bytes_per_ray": alg / max(st_count["rays"], 1),
-                         "note": "scene is L2-resident: the binding limit is SM issue/latency, not HBM (DESIGN.md)"},
+                         "traffic_note": "dram__bytes_read+write per launch of the dominant kernel from profiles/ (ncu --set full); "
+                                         "far BELOW the algorithmic bytes because the scene is L2/L1-resident",
+                         # secondary, physically binding roofline: thread-instructions
+                         "issue": {"achieved": algorithmic_ops(st_count) / (k_ms * 1e-3) / 1e12, "unit": "T thread-op/s",
+                                   "peak": sm_count * 4 * 32 * (clocks["sm_mhz"] or 1965.0) * 1e6 / 1e12,
+                                   "frac": algorithmic_ops(st_count) / (k_ms * 1e-3) / (sm_count * 4 * 32 * (clocks["sm_mhz"] or 1965.0) * 1e6)},
+                         "note": "scene is L2-resident: the binding units are the L1 data pipe (divergent node fetches) and SM "
+                                 "issue slots under SIMT divergence, not HBM (ncu: DESIGN.md 6, profiles/)"},
         }
         if not args.no_cpu:
             st = cpu_render(scene, W, H, args.cpu_spp)

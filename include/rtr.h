@@ -129,7 +129,10 @@ typedef struct rtr_scene_desc {
 enum { RTR_KERNEL_AUTO = 0, RTR_KERNEL_MEGAKERNEL = 1, RTR_KERNEL_WAVEFRONT = 2 };
 enum {
     RTR_FLAG_EXHAUSTIVE = 1u, /* traverse like the reference: both children, no t-culling */
-    RTR_FLAG_COUNT_WORK = 2u  /* also count nodes / primitive tests / env lookups into rtr_stats */
+    RTR_FLAG_COUNT_WORK = 2u, /* also count nodes / primitive tests / env lookups into rtr_stats */
+    RTR_FLAG_REFERENCE_TREE = 4u /* walk the reference's own BVH topology (bvh.rs:59-144) instead of the
+                                    traversal tree built over the same gate boxes; same results, used to count
+                                    work on the reference topology and to validate the traversal tree */
 };
 
 typedef struct rtr_render_params {

@@ -18,6 +18,7 @@ BG_UNIFORM, BG_GRADIENT, BG_SKYMAP = range(3)
 KERNEL_AUTO, KERNEL_MEGAKERNEL, KERNEL_WAVEFRONT = range(3)
 FLAG_EXHAUSTIVE = 1
 FLAG_COUNT_WORK = 2
+FLAG_REFERENCE_TREE = 4
 
 f32, u32, u64, f64 = C.c_float, C.c_uint32, C.c_uint64, C.c_double
 

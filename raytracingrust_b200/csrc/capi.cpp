@@ -52,6 +52,7 @@ struct rtr_scene {
     uint64_t device_bytes = 0, h2d_bytes = 0;
     double build_ms = 0.0;
     uint32_t n_nodes = 0, max_depth = 0;
+    uint32_t root_entry_reference = 0xFFFFFFFFu;
 };
 
 static rtr_status fail(rtr_context* ctx, rtr_status st, const std::string& msg) {
@@ -247,6 +248,7 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     }
     v.background = flat.background;
     v.root_entry = flat.root_entry;
+    s->root_entry_reference = flat.root_entry_reference;
     v.n_objects = (uint32_t)flat.objects.size();
     v.n_materials = (uint32_t)flat.materials.size();
     v.n_volumes = (uint32_t)flat.volumes.size();
@@ -276,6 +278,13 @@ rtr_status rtr_scene_info(const rtr_scene* s, uint64_t* device_bytes, uint64_t* 
     if (n_nodes) *n_nodes = s->n_nodes;
     if (max_depth) *max_depth = s->max_depth;
     return RTR_OK;
+}
+
+// the scene as a launch sees it: traversal tree by default, the reference topology on request
+static SceneView view_for(const rtr_scene* scene, uint32_t flags) {
+    SceneView v = scene->view;
+    if (flags & RTR_FLAG_REFERENCE_TREE) { v.root_entry = scene->root_entry_reference; v.reference_tree = 1u; }
+    return v;
 }
 
 // ------------------------------------------------------------------ render
@@ -321,7 +330,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     const uint64_t n_pixels = (uint64_t)W * H;
     WfArgs a;
     std::memset(&a, 0, sizeof(a));
-    a.sc = scene->view;
+    a.sc = view_for(scene, p->flags);
     a.cam = ray_origin(p->camera);
     a.width = W; a.height = H; a.n_pixels = (uint32_t)n_pixels;
     a.max_ray_depth = p->settings.max_ray_depth;
@@ -426,7 +435,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     const bool count_work = stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0;
     RenderArgs a;
     std::memset(&a, 0, sizeof(a));
-    a.sc = scene->view;
+    a.sc = view_for(scene, p->flags);
     a.cam = ray_origin(p->camera);
     a.width = W; a.height = H;
     a.max_ray_depth = p->settings.max_ray_depth;
@@ -555,7 +564,7 @@ rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_r
     CU(cudaMemcpyAsync(ctx->batch_in, rays, n * sizeof(rtr_ray), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(launch_trace_batch(scene->view, (const rtr_ray*)ctx->batch_in, n, tmin, enable_bvh_tree,
+    CU(launch_trace_batch(view_for(scene, flags), (const rtr_ray*)ctx->batch_in, n, tmin, enable_bvh_tree,
                           (flags & RTR_FLAG_EXHAUSTIVE) != 0, (uint32_t)seed, (uint32_t)(seed >> 32),
                           (rtr_hit*)ctx->batch_out, ctx->stats, ctx->stream));
     CU(cudaEventRecord(ctx->ev1, ctx->stream));

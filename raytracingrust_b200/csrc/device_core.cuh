@@ -267,8 +267,11 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
     uint32_t lref = __float_as_uint(q0.w), rref = __float_as_uint(q1.w);
     float le = -RTR_INF, re = -RTR_INF;
     bool lh = lref != REF_EMPTY_VALUE, rh = rref != REF_EMPTY_VALUE;
-    if (RTR_REF_KIND(lref) == REF_NODE) { lh = slab(q0, q1, r, inv, tmin, tmax, le); if (COUNT) cnt->nodes++; }
-    if (RTR_REF_KIND(rref) == REF_NODE) { rh = slab(q2, q3, r, inv, tmin, tmax, re); if (COUNT) cnt->nodes++; }
+    // traversal tree: every child slot carries a box (a leaf's slot holds its gate, flat.h); reference
+    // topology: leaves carry none (bvh.rs:157-159) and are tested as soon as the parent's box was pierced
+    const bool boxed_leaves = sc.reference_tree == 0u;
+    if (lh && (boxed_leaves || RTR_REF_KIND(lref) == REF_NODE)) { lh = slab(q0, q1, r, inv, tmin, tmax, le); if (COUNT) cnt->nodes++; }
+    if (rh && (boxed_leaves || RTR_REF_KIND(rref) == REF_NODE)) { rh = slab(q2, q3, r, inv, tmin, tmax, re); if (COUNT) cnt->nodes++; }
     if (!EXHAUSTIVE) {
         const float lim = cull_limit(best.t);
         lh = lh && !(le > lim);
@@ -305,6 +308,24 @@ __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, in
         float t;
         if (COUNT) cnt->spheres++;
         if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(cur)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
+    } else if (kind == REF_TRI2) {  // two sibling triangles behind one gate (traversal tree)
+        const uint32_t i = RTR_REF_INDEX(cur);
+        const F4* q = sc.tris + (size_t)i * 4;
+        float4 a0, a1, b0, b1;
+        if (!NESTED) { ldg8(q, a0, a1); ldg8(q + 4, b0, b1); }
+        else { a0 = ldg4(q); a1 = ldg4(q + 1); b0 = ldg4(q + 4); b1 = ldg4(q + 5); }
+        const float4 a2 = ldg4(q + 2), b2 = ldg4(q + 6);
+        float t, u, v;
+        if (COUNT) cnt->tris += 2;
+        if (triangle_t(a0, a1, a2, r, tmin, t, u, v)) offer(sc, best, t, RTR_MAKE_REF(REF_TRI, i), u, v);
+        if (triangle_t(b0, b1, b2, r, tmin, t, u, v)) offer(sc, best, t, RTR_MAKE_REF(REF_TRI, i + 1), u, v);
+    } else if (kind == REF_SPHERE2) {
+        const uint32_t i = RTR_REF_INDEX(cur);
+        const float4 s0 = ldg4(sc.spheres + i), s1 = ldg4(sc.spheres + i + 1);
+        float t;
+        if (COUNT) cnt->spheres += 2;
+        if (sphere_t(s0, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i), 0.0f, 0.0f);
+        if (sphere_t(s1, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i + 1), 0.0f, 0.0f);
     } else if (!NESTED && kind == REF_VOLUME) {
         const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
         float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack.nested(sp), EXHAUSTIVE, COUNT ? cnt : nullptr);
@@ -354,8 +375,9 @@ static __device__ __noinline__ float volume_hit(const SceneView& sc, const Volum
                                          bool exhaustive, Counters* cnt) {
     const float NONE = __int_as_float(0x7fc00000);
     float t1, t2;
-    if (!boundary_t(sc, vol.entry, r, inv, -RTR_INF, stack, exhaustive, cnt, t1)) return NONE;
-    if (!boundary_t(sc, vol.entry, r, inv, t1 + tmin, stack, exhaustive, cnt, t2)) return NONE;
+    const uint32_t entry = sc.reference_tree ? vol.entry_reference : vol.entry;
+    if (!boundary_t(sc, entry, r, inv, -RTR_INF, stack, exhaustive, cnt, t1)) return NONE;
+    if (!boundary_t(sc, entry, r, inv, t1 + tmin, stack, exhaustive, cnt, t2)) return NONE;
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return NONE;
@@ -381,7 +403,7 @@ __device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, cons
     }
     float closest = RTR_INF;  // closest_so_far (scene.rs:144)
     for (uint32_t i = 0; i < sc.n_objects; ++i) {
-        const uint32_t entry = sc.objects[i].entry;
+        const uint32_t entry = sc.reference_tree ? sc.objects[i].entry_reference : sc.objects[i].entry;
         const uint32_t kind = RTR_REF_KIND(entry);
         if (kind == REF_SPHERE) {
             float t;

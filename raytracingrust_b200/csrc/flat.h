@@ -28,6 +28,8 @@ enum : uint32_t {
     REF_SPHERE = 1u,  // slot in spheres[] / sphere_info[]
     REF_TRI = 2u,     // slot in tris[] (x4) / tri_vn[] (x3)
     REF_VOLUME = 3u,  // index in volumes[]
+    REF_TRI2 = 4u,    // traversal tree only: triangle slots i and i+1, siblings under one reference Split (one gate)
+    REF_SPHERE2 = 5u, // traversal tree only: sphere slots i and i+1, likewise
     REF_EMPTY = 7u    // BvhNode::None
 };
 #define RTR_REF_KIND(r) ((r) >> 29)
@@ -51,12 +53,14 @@ struct VolumeRec {        // Volume (lib/volume.rs:19-31)
     uint32_t object;      // Scene.objects index
     uint32_t rank;        // DFS leaf rank of the volume leaf
     uint32_t index;       // index in rtr_scene_desc.volumes (RNG iteration slot)
-    uint32_t _pad[2];
+    uint32_t entry_reference;  // the boundary in the reference topology (RTR_FLAG_REFERENCE_TREE)
+    uint32_t _pad;
 };
 
 struct ObjectRec {        // Scene.objects[i], for the BVH-off linear scan (scene.rs:141-156)
     uint32_t entry;       // SPHERE slot | NODE (pseudo parent) | TRI | VOLUME | EMPTY
-    uint32_t _pad[3];
+    uint32_t entry_reference;  // the same in the reference topology
+    uint32_t _pad[2];
 };
 
 struct MaterialRec {      // Box<dyn Material>
@@ -87,7 +91,8 @@ struct SceneView {
     const MaterialRec* materials;
     const F4* env;            // SkyMap texels as float4 (rgb, 0)
     BackgroundRec background;
-    uint32_t root_entry;      // entry ref of the scene tree
+    uint32_t root_entry;      // entry ref of the scene tree being walked (traversal tree, or the reference topology)
+    uint32_t reference_tree;  // 1: walk the reference topology (leaf slots carry no box) — counting / validation
     uint32_t n_objects;
     uint32_t n_materials;
     uint32_t n_volumes;

@@ -44,11 +44,20 @@ inline Box epsilon_expand(Box b, float eps) {  // aabb.rs:57-78
 }
 
 struct Built {
-    uint32_t ref;   // child reference as stored in the parent
+    uint32_t ref;   // child reference as stored in the parent (REFERENCE topology)
     Box box;        // own box (valid iff split)
     bool split;
     uint32_t depth; // levels below and including this node
+    // the same subtree in the TRAVERSAL tree (see build_traversal): equal to `ref` for a primitive
+    uint32_t fast_ref = 0xFFFFFFFFu;
+    uint32_t fast_depth = 0;
+    bool leaf = false;  // came from Collection::leaf (BvhNode::Object), not from a split of this collection
+    Built() : ref(0xFFFFFFFFu), box{}, split(false), depth(0) {}
+    Built(uint32_t r, Box b, bool s, uint32_t d) : ref(r), box(b), split(s), depth(d), fast_ref(r), fast_depth(d) {}
 };
+
+// one leaf of a collection as the traversal tree sees it: what to visit, and the box that GATES the visit
+struct GatedLeaf { uint32_t ref; Box gate; uint32_t depth; };
 
 // Anything BvhNode::from_list can be built over (bvh.rs:18-28)
 struct Collection {
@@ -71,21 +80,131 @@ struct Flattener {
         return idx;
     }
     static float bits(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
-    void write_node(uint32_t idx, const Built& l, const Built& r) {
+    void write_node_raw(uint32_t idx, uint32_t lref, const Box& lb, uint32_t rref, const Box& rb) {
         F4* q = &out.nodes[(size_t)idx * 4];
-        Box lb = l.split ? l.box : Box{{0, 0, 0}, {0, 0, 0}};
-        Box rb = r.split ? r.box : Box{{0, 0, 0}, {0, 0, 0}};
-        q[0] = F4{lb.min.x, lb.min.y, lb.min.z, bits(l.ref)};
-        q[1] = F4{lb.max.x, lb.max.y, lb.max.z, bits(r.ref)};
+        q[0] = F4{lb.min.x, lb.min.y, lb.min.z, bits(lref)};
+        q[1] = F4{lb.max.x, lb.max.y, lb.max.z, bits(rref)};
         q[2] = F4{rb.min.x, rb.min.y, rb.min.z, 0.0f};
         q[3] = F4{rb.max.x, rb.max.y, rb.max.z, 0.0f};
     }
+    void write_node(uint32_t idx, const Built& l, const Built& r) {
+        const Box zero{{0, 0, 0}, {0, 0, 0}};
+        write_node_raw(idx, l.ref, l.split ? l.box : zero, r.ref, r.split ? r.box : zero);
+    }
+
+    // ---- traversal tree ------------------------------------------------------------------------------
+    // The reference tests a leaf of a collection exactly when the box of the Split that holds it is pierced
+    // (bvh.rs:157-163; leaves carry no box, Q3) — ancestors above that Split contain it, and the slab test is
+    // monotone under containment for a fixed ray, so "parent box pierced" already implies every ancestor's.
+    // That parent box is the leaf's GATE.  Any tree whose interior boxes are unions of the gates below them
+    // and whose leaf slots carry the gate therefore visits the same candidate set as the reference topology,
+    // and ties are still decided by the reference's DFS leaf rank stored with each primitive.  This frees the
+    // topology: the traversal tree is a binned-SAH tree over the gates (the reference's object-median split on
+    // centroids costs ~2x the node visits on the mesh scenes), depth-capped so the stack bound holds.
+    static float half_area(const Box& b) {
+        const float dx = b.max.x - b.min.x, dy = b.max.y - b.min.y, dz = b.max.z - b.min.z;
+        return dx * dy + dy * dz + dz * dx;
+    }
+    struct FastOut { uint32_t ref; Box box; uint32_t depth; };
+    FastOut build_traversal(std::vector<GatedLeaf>& L, size_t lo, size_t hi, uint32_t depth_left) {
+        const size_t n = hi - lo;
+        if (n == 1) return FastOut{L[lo].ref, L[lo].gate, L[lo].depth};
+        Box cb{};  // centroid bounds
+        for (size_t i = lo; i < hi; ++i) {
+            const V3 c = centroid(L[i].gate);
+            cb = i == lo ? Box{c, c} : surround(cb, Box{c, c});
+        }
+        size_t mid = lo + n / 2;
+        uint32_t levels_needed = 0;
+        while ((size_t(1) << levels_needed) < n) ++levels_needed;
+        const bool must_balance = levels_needed + 1 >= depth_left;
+        const V3 ext = sub(cb.max, cb.min);
+        const float emax = std::fmax(ext.x, std::fmax(ext.y, ext.z));
+        bool split_done = false;
+        if (!must_balance && emax > 0.0f && n > 2) {
+            constexpr int NB = 16;
+            float best_cost = INFINITY;
+            int best_axis = -1, best_plane = -1;
+            for (int axis = 0; axis < 3; ++axis) {
+                const float e = axis == 0 ? ext.x : axis == 1 ? ext.y : ext.z;
+                if (!(e > 0.0f)) continue;
+                const float mn = axis == 0 ? cb.min.x : axis == 1 ? cb.min.y : cb.min.z;
+                const float scale = (float)NB / e;
+                Box bb[NB] = {}; size_t cnt[NB] = {0};
+                for (size_t i = lo; i < hi; ++i) {
+                    const V3 c = centroid(L[i].gate);
+                    int k = (int)(((axis == 0 ? c.x : axis == 1 ? c.y : c.z) - mn) * scale);
+                    k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
+                    bb[k] = cnt[k] ? surround(bb[k], L[i].gate) : L[i].gate;
+                    ++cnt[k];
+                }
+                float right_area[NB]; size_t right_cnt[NB];
+                Box acc{}; size_t c = 0;
+                for (int k = NB - 1; k > 0; --k) {
+                    if (cnt[k]) { acc = c ? surround(acc, bb[k]) : bb[k]; c += cnt[k]; }
+                    right_area[k] = c ? half_area(acc) : 0.0f; right_cnt[k] = c;
+                }
+                c = 0;
+                for (int k = 0; k < NB - 1; ++k) {
+                    if (cnt[k]) { acc = c ? surround(acc, bb[k]) : bb[k]; c += cnt[k]; }
+                    if (c == 0 || right_cnt[k + 1] == 0) continue;
+                    const float cost = half_area(acc) * (float)c + right_area[k + 1] * (float)right_cnt[k + 1];
+                    if (cost < best_cost) { best_cost = cost; best_axis = axis; best_plane = k; }
+                }
+            }
+            if (best_axis >= 0) {
+                const float e = best_axis == 0 ? ext.x : best_axis == 1 ? ext.y : ext.z;
+                const float mn = best_axis == 0 ? cb.min.x : best_axis == 1 ? cb.min.y : cb.min.z;
+                const float scale = (float)NB / e;
+                auto it = std::stable_partition(L.begin() + lo, L.begin() + hi, [&](const GatedLeaf& g) {
+                    const V3 c = centroid(g.gate);
+                    int k = (int)(((best_axis == 0 ? c.x : best_axis == 1 ? c.y : c.z) - mn) * scale);
+                    k = k < 0 ? 0 : k >= NB ? NB - 1 : k;
+                    return k <= best_plane;
+                });
+                const size_t m = (size_t)(it - L.begin());
+                if (m > lo && m < hi) { mid = m; split_done = true; }
+            }
+        }
+        if (!split_done && emax > 0.0f) {  // balanced fallback: median of the widest centroid axis
+            const int axis = (ext.x >= ext.y && ext.x >= ext.z) ? 0 : (ext.y >= ext.z ? 1 : 2);
+            std::nth_element(L.begin() + lo, L.begin() + mid, L.begin() + hi, [&](const GatedLeaf& a, const GatedLeaf& b) {
+                const V3 ca = centroid(a.gate), cb2 = centroid(b.gate);
+                return (axis == 0 ? ca.x : axis == 1 ? ca.y : ca.z) < (axis == 0 ? cb2.x : axis == 1 ? cb2.y : cb2.z);
+            });
+        }
+        const uint32_t idx = alloc_node();
+        const FastOut l = build_traversal(L, lo, mid, depth_left - 1);
+        const FastOut r = build_traversal(L, mid, hi, depth_left - 1);
+        write_node_raw(idx, l.ref, l.box, r.ref, r.box);
+        return FastOut{RTR_MAKE_REF(REF_NODE, idx), surround(l.box, r.box), 1 + std::max(l.depth, r.depth)};
+    }
+
+    // reference tree + traversal tree of one collection (scene.build_bvh / mesh.build_bvh)
+    Built build_collection(std::vector<uint32_t>& handles, Collection& coll) {
+        const size_t n = handles.size();
+        std::vector<GatedLeaf> gated;
+        gated.reserve(n);
+        Built root = build(handles, coll, &gated);
+        if (!err.empty() || n < 2) return root;  // None / a single Object: both trees are that leaf
+        if (gated.size() == 1) {  // two sibling primitives: one paired leaf gated by the root's own box
+            root.fast_ref = gated[0].ref;
+            root.fast_depth = 1;
+            return root;
+        }
+        uint32_t levels = 0;
+        while ((size_t(1) << levels) < n) ++levels;
+        const FastOut f = build_traversal(gated, 0, gated.size(), levels + 8);
+        root.fast_ref = f.ref;
+        root.fast_depth = f.depth;
+        return root;
+    }
 
     // BvhNode::from_list (bvh.rs:59-144).  `handles` is consumed.
-    Built build(std::vector<uint32_t>& handles, Collection& coll) {
+    Built build(std::vector<uint32_t>& handles, Collection& coll, std::vector<GatedLeaf>* gated) {
         const size_t n = handles.size();
         if (n == 0) return Built{REF_EMPTY_VALUE, Box{}, false, 0};  // BvhNode::None
-        if (n == 1) return coll.leaf(handles[0]);                    // BvhNode::Object
+        if (n == 1) { Built b = coll.leaf(handles[0]); b.leaf = true; return b; }  // BvhNode::Object
         std::vector<Box> b(n);
         for (size_t i = 0; i < n; ++i) b[i] = coll.bounds(handles[i]);
         Box bounds = b[0];                                           // :68-72
@@ -112,11 +231,21 @@ struct Flattener {
         handles.clear(); handles.shrink_to_fit();
         b.clear(); b.shrink_to_fit(); key.clear(); key.shrink_to_fit(); order.clear(); order.shrink_to_fit();
         uint32_t idx = alloc_node();  // pre-order index: a subtree is contiguous in memory
-        Built l = build(left, coll);
+        Built l = build(left, coll, gated);
         if (!err.empty()) return l;
-        Built r = build(right, coll);
+        Built r = build(right, coll, gated);
         if (!err.empty()) return r;
         write_node(idx, l, r);
+        // a leaf child of this Split is gated by this Split's box
+        // (two sibling primitives share the gate and sit in consecutive slots: one paired leaf, one box test)
+        const uint32_t lk = RTR_REF_KIND(l.ref), rk = RTR_REF_KIND(r.ref);
+        if (l.leaf && r.leaf && !l.split && !r.split && lk == rk && (lk == REF_TRI || lk == REF_SPHERE) &&
+            RTR_REF_INDEX(r.ref) == RTR_REF_INDEX(l.ref) + 1) {
+            gated->push_back(GatedLeaf{RTR_MAKE_REF(lk == REF_TRI ? REF_TRI2 : REF_SPHERE2, RTR_REF_INDEX(l.ref)), bounds, 1u});
+        } else {
+            if (l.leaf) gated->push_back(GatedLeaf{traversal_entry(l), bounds, l.fast_depth + (l.split ? 1u : 0u)});
+            if (r.leaf) gated->push_back(GatedLeaf{traversal_entry(r), bounds, r.fast_depth + (r.split ? 1u : 0u)});
+        }
         return Built{RTR_MAKE_REF(REF_NODE, idx), bounds, true, 1 + std::max(l.depth, r.depth)};
     }
 
@@ -127,6 +256,14 @@ struct Flattener {
         uint32_t idx = alloc_node();
         write_node(idx, root, Built{REF_EMPTY_VALUE, Box{}, false, 0});
         *depth = root.depth + 1;
+        return RTR_MAKE_REF(REF_NODE, idx);
+    }
+
+    // the same for the traversal tree: a nested collection (mesh) still tests its own root box on entry
+    uint32_t traversal_entry(const Built& b) {
+        if (!b.split) return b.fast_ref;
+        uint32_t idx = alloc_node();
+        write_node_raw(idx, b.fast_ref, b.box, REF_EMPTY_VALUE, Box{{0, 0, 0}, {0, 0, 0}});
         return RTR_MAKE_REF(REF_NODE, idx);
     }
 
@@ -180,7 +317,7 @@ struct Flattener {
         MeshColl coll(*this, m, object);
         std::vector<uint32_t> handles(m.n_indices / 3);
         for (size_t i = 0; i < handles.size(); ++i) handles[i] = (uint32_t)i;
-        return build(handles, coll);  // mesh.build_bvh() (mesh.rs:119-121)
+        return build_collection(handles, coll);  // mesh.build_bvh() (mesh.rs:119-121)
     }
 
     Box object_bounds(rtr_object_ref ref) const {
@@ -221,8 +358,9 @@ struct Flattener {
         rec.rank = rank++;
         uint32_t bdepth = 0;
         Built b = emit_object(v.boundary, object);
-        rec.entry = make_entry(b, &bdepth);
-        out.max_boundary_depth = std::max(out.max_boundary_depth, bdepth);
+        rec.entry_reference = make_entry(b, &bdepth);
+        rec.entry = traversal_entry(b);
+        out.max_boundary_depth = std::max(out.max_boundary_depth, std::max(bdepth, b.fast_depth + 1));
         rec.neg_inv_density = v.neg_inv_density;  // as stored by Volume::new (volume.rs:26-31)
         rec.material = v.boundary.kind == RTR_OBJ_SPHERE ? d.spheres[v.boundary.index].material
                                                          : d.meshes[v.boundary.index].material;
@@ -291,11 +429,12 @@ int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err) {
     Flattener::SceneColl coll(f);
     std::vector<uint32_t> handles(d.n_objects);
     for (uint32_t i = 0; i < d.n_objects; ++i) handles[i] = i;
-    Built root = f.build(handles, coll);  // scene.build_bvh() (scene.rs:112-114)
+    Built root = f.build_collection(handles, coll);  // scene.build_bvh() (scene.rs:112-114)
     if (!err.empty()) return RTR_INVALID_ARG;
     uint32_t depth = 0;
-    out.root_entry = f.make_entry(root, &depth);
-    out.max_depth = depth;
+    out.root_entry_reference = f.make_entry(root, &depth);
+    out.root_entry = f.traversal_entry(root);
+    out.max_depth = std::max(depth, root.fast_depth + 1);
 
     // linear-scan table (scene.rs:141-156): one entry per object, in add_object order.  A mesh
     // root that is a Split needs its own box tested on entry -> pseudo parent per mesh object.
@@ -303,7 +442,8 @@ int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err) {
     for (uint32_t i = 0; i < d.n_objects; ++i) {
         std::memset(&out.objects[i], 0, sizeof(ObjectRec));
         uint32_t dd = 0;
-        out.objects[i].entry = f.make_entry(coll.built[i], &dd);
+        out.objects[i].entry_reference = f.make_entry(coll.built[i], &dd);
+        out.objects[i].entry = f.traversal_entry(coll.built[i]);
     }
     out.materials.resize(d.n_materials);
     for (uint32_t i = 0; i < d.n_materials; ++i) {

@@ -17,7 +17,8 @@ struct HostFlat {
     std::vector<ObjectRec> objects;
     std::vector<MaterialRec> materials;
     BackgroundRec background;
-    uint32_t root_entry = 0xFFFFFFFFu;
+    uint32_t root_entry = 0xFFFFFFFFu;            // traversal tree
+    uint32_t root_entry_reference = 0xFFFFFFFFu;  // reference topology
     uint32_t max_depth = 0;           // levels of the fused scene tree incl. the pseudo parent
     uint32_t max_boundary_depth = 0;  // deepest volume-boundary tree
 };

@@ -130,4 +130,4 @@ def test_error_statuses(ctx):
 
 def test_scene_info(ctx):
     info = ctx.upload(_scenes.simple()).info()
-    assert info["n_nodes"] == 102 and 7 <= info["max_depth"] <= 9 and info["h2d_bytes"] > 102 * 64
+    assert 102 < info["n_nodes"] <= 2 * 102 and 7 <= info["max_depth"] <= 16 and info["h2d_bytes"] > 102 * 64

@@ -35,6 +35,9 @@ def test_bvh_closest_hit(ctx, name):
     ulp = 4 if name == "volumes" else 0
     n_hit = assert_hits_identical(dev, ora, f"{name} culled", ulp)
     assert_hits_identical(ds.trace_batch(rays, enable_bvh_tree=True, seed=11, flags=A.FLAG_EXHAUSTIVE), ora, f"{name} exhaustive", ulp)
+    # the same two walks over the reference's own topology (the default walks the gate-box traversal tree)
+    for flags in (A.FLAG_REFERENCE_TREE, A.FLAG_REFERENCE_TREE | A.FLAG_EXHAUSTIVE):
+        assert_hits_identical(ds.trace_batch(rays, enable_bvh_tree=True, seed=11, flags=flags), ora, f"{name} reference tree {flags}", ulp)
     assert n_hit > 100 and st["rays"] == len(rays)
 
 
@@ -44,18 +47,21 @@ def test_linear_scan_closest_hit(ctx, name):
     scene = SCENES[name]()
     rays = ray_set(scene)
     ora = orc.OracleScene(scene).trace_batch(rays, enable_bvh_tree=False, seed=2)
-    dev = ctx.upload(scene).trace_batch(rays, enable_bvh_tree=False, seed=2)
-    assert_hits_identical(dev, ora, f"{name} linear", 4 if name == "volumes" else 0)
+    ds = ctx.upload(scene)
+    for flags in (0, A.FLAG_REFERENCE_TREE, A.FLAG_EXHAUSTIVE):
+        dev = ds.trace_batch(rays, enable_bvh_tree=False, seed=2, flags=flags)
+        assert_hits_identical(dev, ora, f"{name} linear flags={flags}", 4 if name == "volumes" else 0)
 
 
 def test_work_counters_match_counting_walk(ctx):
-    """The device's culled walk does the algorithmic work SURVEY 8(d) defines (same ordered traversal,
-    up to near/far ties and the culling slack): counters within 2 % of the oracle's counting walk."""
+    """On the reference topology (RTR_FLAG_REFERENCE_TREE) the device's culled walk does the algorithmic work
+    SURVEY 8(d) defines (same ordered traversal, up to near/far ties and the culling slack): counters within 2 %
+    of the oracle's counting walk.  The default traversal tree tests the same primitives' gates with fewer boxes."""
     for name in ("simple", "monkey", "grid8000"):
         scene = SCENES[name]()
         rays = ray_set(scene)
         counts, _ = orc.OracleScene(scene).count_batch(rays)
-        _, st = ctx.upload(scene).trace_batch(rays, want_stats=True)
+        _, st = ctx.upload(scene).trace_batch(rays, want_stats=True, flags=A.FLAG_REFERENCE_TREE)
         for k_dev, k_ora in (("nodes_visited", "nodes"), ("tri_tests", "tris"), ("sphere_tests", "spheres")):
             if counts[k_ora]:
                 assert abs(st[k_dev] - counts[k_ora]) <= 0.02 * counts[k_ora] + 16, (name, k_dev, st[k_dev], counts[k_ora])
@@ -124,6 +130,8 @@ def test_full_size_culled_equals_exhaustive_1m_spheres(ctx):
     h = ds.trace_batch(primary)
     hx = ds.trace_batch(primary, flags=A.FLAG_EXHAUSTIVE)
     assert np.array_equal(h, hx)
+    # ... and the gate-box traversal tree returns exactly what a walk of the reference's own topology returns
+    assert np.array_equal(h, ds.trace_batch(primary, flags=A.FLAG_REFERENCE_TREE))
     hit = h["object"] != A.RTR_NO_HIT
     assert hit.mean() > 0.3
     rng = np.random.default_rng(1)
@@ -134,6 +142,7 @@ def test_full_size_culled_equals_exhaustive_1m_spheres(ctx):
     secondary["direction"] = np.where(hit[:, None], h["normal"] + u, u)
     h2 = ds.trace_batch(secondary)
     assert np.array_equal(h2, ds.trace_batch(secondary, flags=A.FLAG_EXHAUSTIVE))
+    assert np.array_equal(h2, ds.trace_batch(secondary, flags=A.FLAG_REFERENCE_TREE | A.FLAG_EXHAUSTIVE))
     sel = rng.choice(len(primary), 1 << 15, replace=False)
     os_ = orc.OracleScene(scene)
     assert_hits_identical(h[sel], os_.trace_batch(primary[sel]), "1M primary sample")
