@@ -147,6 +147,9 @@ def main():
     ap.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU sample")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--kernel", type=int, default=0)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank renders the workload's spp (image has N x spp samples); strong: the workload's "
+                         "spp is split across ranks (BASELINE config 5 sweep)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -177,18 +180,22 @@ def main():
     info = dev_scene.info()
     accum = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
     rgba = torch.empty((H, W, 4), dtype=torch.uint8, device="cuda")
-    # weak scaling: rank r renders global samples [r*spp, (r+1)*spp); the image has world*spp samples
-    params = rt.make_params(scene, W, H, seed=0, sample_begin=rank * spp, sample_count=spp, kernel=args.kernel)
+    # weak scaling: rank r renders global samples [r*spp, (r+1)*spp); the image has world*spp samples.
+    # strong scaling: the image keeps spp samples, rank r renders its balanced slice of them.
+    from raytracingrust_b200.distributed import sample_slice
+    total_spp = spp * world if args.scaling == "weak" else spp
+    s_begin, s_count = (rank * spp, spp) if args.scaling == "weak" else sample_slice(spp, rank, world)
+    params = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel)
 
     def step():
         dev_scene.render_accumulate_device(params, accum.data_ptr(), want_stats=False)
         if world > 1:
             dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)  # one NCCL reduce over NVLink
         if rank == 0:
-            ctx.resolve_device(accum.data_ptr(), W, H, spp * world, rgba.data_ptr())
+            ctx.resolve_device(accum.data_ptr(), W, H, total_spp, rgba.data_ptr())
 
     # rays per step and work counters (untimed, counting variant of the kernel)
-    pc = rt.make_params(scene, W, H, seed=0, sample_begin=rank * spp, sample_count=spp, kernel=args.kernel,
+    pc = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel,
                         flags=A.FLAG_COUNT_WORK | A.FLAG_REFERENCE_TREE)  # algorithmic work is DEFINED on the reference topology
     st_count = dev_scene.render_accumulate_device(pc, accum.data_ptr(), want_stats=True)
     for _ in range(args.warmup):
@@ -220,12 +227,12 @@ def main():
         ms, rays_step = float(tmax[0]), float(tsum[1])
     else:
         rays_step = float(t[1])
-    samples_step = float(W) * H * spp * world
+    samples_step = float(W) * H * total_spp
 
     # end to end through the reference-facing call: upload (H2D) + render + RGBA8 D2H, host buffers
     host_rgba = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
     lowered = scene.lower()
-    pe = rt.make_params(scene, W, H, seed=0, sample_begin=rank * spp, sample_count=spp, kernel=args.kernel)
+    pe = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel)
     e2e_steps = max(1, min(args.steps, 3))
     torch.cuda.synchronize()
     if world > 1:
@@ -261,10 +268,10 @@ def main():
         out = {
             "metric": "Mrays/s", "value": rays_step * args.steps / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "msamples_per_s": samples_step * args.steps / (ms * 1e-3) / 1e6,
             "rays_per_step": rays_step, "samples_per_step": samples_step,
-            "config": {"workload": desc, "kernel": {1: "megakernel", 2: "wavefront"}[st_count["kernel_used"]], "per_gpu_spp": spp, "parallelism": f"sample-slices x{world} + ncclReduce",
+            "config": {"workload": desc, "kernel": {1: "megakernel", 2: "wavefront"}[st_count["kernel_used"]], "per_gpu_spp": s_count, "image_spp": total_spp, "parallelism": f"sample-slices x{world} + ncclReduce",
                        "l2_policy": "each step rewrites the 33 MB accumulation buffer and traces fresh Philox paths; scene working set is L2-resident by design (SURVEY 8d)",
                        "scene_device_bytes": info["device_bytes"], "bvh_nodes": info["n_nodes"]},
             "clocks": clocks,

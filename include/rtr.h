@@ -130,6 +130,8 @@ enum { RTR_KERNEL_AUTO = 0, RTR_KERNEL_MEGAKERNEL = 1, RTR_KERNEL_WAVEFRONT = 2 
 enum {
     RTR_FLAG_EXHAUSTIVE = 1u, /* traverse like the reference: both children, no t-culling */
     RTR_FLAG_COUNT_WORK = 2u, /* also count nodes / primitive tests / env lookups into rtr_stats */
+    RTR_FLAG_ACCUMULATE = 8u, /* rtr_render_accumulate_device ADDS this sample slice to accum_dev instead of
+                                 overwriting it: progressive rendering (the GUI's continuous mode, src/gui.rs:333-337) */
     RTR_FLAG_REFERENCE_TREE = 4u /* walk the reference's own BVH topology (bvh.rs:59-144) instead of the
                                     traversal tree built over the same gate boxes; same results, used to count
                                     work on the reference topology and to validate the traversal tree */
@@ -255,6 +257,10 @@ typedef struct rtr_host_mesh rtr_host_mesh;
 rtr_status rtr_mesh_load_obj(const char* path, uint32_t material, rtr_host_mesh** out);
 const rtr_mesh* rtr_host_mesh_get(const rtr_host_mesh* hm);
 void rtr_host_mesh_destroy(rtr_host_mesh* hm);
+
+/* ---- headless output (replaces the window blit of RenderTarget.data, src/main.rs:92-97) ---- */
+/* 8-bit RGBA PNG of a host RGBA8 buffer as rtr_render fills it */
+rtr_status rtr_write_png(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
 
 #ifdef __cplusplus
 }

@@ -19,6 +19,7 @@ KERNEL_AUTO, KERNEL_MEGAKERNEL, KERNEL_WAVEFRONT = range(3)
 FLAG_EXHAUSTIVE = 1
 FLAG_COUNT_WORK = 2
 FLAG_REFERENCE_TREE = 4
+FLAG_ACCUMULATE = 8
 
 f32, u32, u64, f64 = C.c_float, C.c_uint32, C.c_uint64, C.c_double
 
@@ -139,4 +140,5 @@ EXPORTED_SYMBOLS = [
     "rtr_trace_batch", "rtr_scatter_batch", "rtr_background_batch", "rtr_camera_rays",
     "rtr_scene_load_json", "rtr_host_scene_desc", "rtr_host_scene_camera", "rtr_host_scene_settings",
     "rtr_host_scene_destroy", "rtr_mesh_load_obj", "rtr_host_mesh_get", "rtr_host_mesh_destroy",
+    "rtr_write_png",
 ]

@@ -240,7 +240,24 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     step(upload(s, flat.volumes, &v.volumes, ctx->stream));
     step(upload(s, flat.objects, &v.objects, ctx->stream));
     step(upload(s, flat.materials, &v.materials, ctx->stream));
-    step(upload(s, flat.env, &v.env, ctx->stream));
+    {   // SkyMap texels: raw RGB goes up as it is, the float4 layout is produced on the device
+        const size_t n_tex = desc->background.kind == RTR_BG_SKYMAP ? (size_t)desc->background.width * desc->background.height : 0;
+        void* env = nullptr;
+        float* raw = nullptr;
+        step(cudaMalloc(&env, (n_tex ? n_tex : 1) * sizeof(float4)));
+        if (env) { s->allocs.push_back(env); s->device_bytes += (n_tex ? n_tex : 1) * sizeof(float4); }
+        v.env = (const F4*)env;
+        if (n_tex && e == cudaSuccess) {
+            step(cudaMalloc((void**)&raw, n_tex * 3 * sizeof(float)));
+            if (raw) {
+                step(cudaMemcpyAsync(raw, desc->background.texels, n_tex * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+                step(launch_expand_env(raw, (float4*)env, n_tex, ctx->stream));
+                s->h2d_bytes += n_tex * 3 * sizeof(float);
+                step(cudaStreamSynchronize(ctx->stream));
+                cudaFree(raw);
+            }
+        }
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);  // host vectors die at return
     if (e != cudaSuccess) {
         rtr_scene_destroy(s);
@@ -340,6 +357,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
     a.sample_begin = p->sample_begin; a.sample_end = p->sample_begin + count;
     a.refill_threshold = ctx->wf_refill_threshold;
+    a.accumulate = (p->flags & RTR_FLAG_ACCUMULATE) ? 1u : 0u;
     // samples of every pixel in flight per wave: enough paths to fill the chip, bounded scratch
     uint64_t ws = n_pixels ? ctx->wf_target_paths / n_pixels : 1;
     if (ws < 1) ws = 1;
@@ -459,6 +477,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
         a.n_chunks = (count + a.chunk_samples - 1) / a.chunk_samples;
     }
     a.refill_threshold = ctx->refill_threshold;
+    a.accumulate = (p->flags & RTR_FLAG_ACCUMULATE) ? 1u : 0u;
     a.accum = accum_dev;
     if (a.n_chunks > 1) {
         CU(grow(&ctx->partials, &ctx->partials_elems, (size_t)a.n_chunks * W * H));
@@ -478,7 +497,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
         CU(launch_megakernel(a, (int)blocks, exhaustive, count_work, ctx->stream));
         ++launches;
         if (a.n_chunks > 1) {
-            CU(launch_sum_chunks(a.partials, accum_dev, W * H, a.n_chunks, ctx->stream));
+            CU(launch_sum_chunks(a.partials, accum_dev, W * H, a.n_chunks, a.accumulate != 0, ctx->stream));
             ++launches;
         }
     }

@@ -460,10 +460,8 @@ int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err) {
     out.background.br = d.background.bottom.x; out.background.bg = d.background.bottom.y; out.background.bb = d.background.bottom.z;
     if (d.background.kind == RTR_BG_SKYMAP) {
         out.background.width = d.background.width; out.background.height = d.background.height;
-        size_t n = (size_t)d.background.width * d.background.height;
-        out.env.resize(n);
-        for (size_t k = 0; k < n; ++k)
-            out.env[k] = F4{d.background.texels[3 * k], d.background.texels[3 * k + 1], d.background.texels[3 * k + 2], 0.0f};
+        // texels are expanded RGB -> float4 on the device (capi.cpp: expand_env), not here: the host loop over a
+        // 4096x2048 map cost more than the whole H2D copy
     }
     return RTR_OK;
 }

@@ -380,3 +380,45 @@ const rtr_mesh* rtr_host_mesh_get(const rtr_host_mesh* hm) { return hm ? &hm->me
 void rtr_host_mesh_destroy(rtr_host_mesh* hm) { delete hm; }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ headless output
+// The reference only ever shows RenderTarget.data in a window (src/main.rs:92-97); without a graphics stack the
+// RGBA8 buffer is written to a file instead.  Minimal PNG: 8-bit RGBA, filter 0 on every row, zlib deflate.
+#include <zlib.h>
+
+extern "C" rtr_status rtr_write_png(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height) {
+    if (!path || (!rgba8 && width && height)) { rtr::set_global_error("rtr_write_png: null argument"); return RTR_INVALID_ARG; }
+    if (width == 0 || height == 0) { rtr::set_global_error("rtr_write_png: empty image"); return RTR_INVALID_ARG; }
+    std::vector<unsigned char> raw((size_t)height * ((size_t)width * 4 + 1));
+    for (uint32_t y = 0; y < height; ++y) {
+        unsigned char* row = &raw[(size_t)y * ((size_t)width * 4 + 1)];
+        row[0] = 0;  // filter type None
+        std::memcpy(row + 1, rgba8 + (size_t)y * width * 4, (size_t)width * 4);
+    }
+    uLongf zlen = compressBound((uLong)raw.size());
+    std::vector<unsigned char> z(zlen);
+    if (compress2(z.data(), &zlen, raw.data(), (uLong)raw.size(), 6) != Z_OK) { rtr::set_global_error("rtr_write_png: deflate failed"); return RTR_IO_ERROR; }
+    FILE* f = std::fopen(path, "wb");
+    if (!f) { rtr::set_global_error(std::string("rtr_write_png: cannot open ") + path); return RTR_IO_ERROR; }
+    auto be32 = [](unsigned char* p, uint32_t v) { p[0] = (unsigned char)(v >> 24); p[1] = (unsigned char)(v >> 16); p[2] = (unsigned char)(v >> 8); p[3] = (unsigned char)v; };
+    bool ok = true;
+    auto chunk = [&](const char* type, const unsigned char* data, uint32_t len) {
+        unsigned char hdr[8];
+        be32(hdr, len); std::memcpy(hdr + 4, type, 4);
+        uLong c = crc32(0L, (const Bytef*)hdr + 4, 4);
+        if (len) c = crc32(c, data, len);
+        unsigned char tail[4]; be32(tail, (uint32_t)c);
+        ok = ok && std::fwrite(hdr, 1, 8, f) == 8 && (len == 0 || std::fwrite(data, 1, len, f) == len) && std::fwrite(tail, 1, 4, f) == 4;
+    };
+    static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    ok = std::fwrite(sig, 1, 8, f) == 8;
+    unsigned char ihdr[13];
+    be32(ihdr, width); be32(ihdr + 4, height);
+    ihdr[8] = 8; ihdr[9] = 6; ihdr[10] = 0; ihdr[11] = 0; ihdr[12] = 0;  // 8-bit, RGBA, deflate, adaptive, no interlace
+    chunk("IHDR", ihdr, 13);
+    chunk("IDAT", z.data(), (uint32_t)zlen);
+    chunk("IEND", nullptr, 0);
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) { rtr::set_global_error("rtr_write_png: write failed"); return RTR_IO_ERROR; }
+    return RTR_OK;
+}

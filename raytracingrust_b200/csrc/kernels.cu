@@ -149,7 +149,9 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_
         if (valid) {
             const float n = s_first < s_end ? (float)(s_end - s_first) : 0.0f;
             float4* dst = a.n_chunks == 1 ? a.accum : a.partials + (size_t)chunk * a.width * a.height;
-            dst[pixel] = make_float4(sum.x, sum.y, sum.z, n);
+            float4 o = make_float4(sum.x, sum.y, sum.z, n);
+            if (a.accumulate && a.n_chunks == 1) { const float4 p = dst[pixel]; o.x = p.x + o.x; o.y = p.y + o.y; o.z = p.z + o.z; o.w = p.w + o.w; }
+            dst[pixel] = o;
         }
         n_rays += rays;
         if (COUNT) { n_nodes += cnt.nodes; n_tris += cnt.tris; n_spheres += cnt.spheres; n_env += cnt.env; }
@@ -176,10 +178,11 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_
     }
 }
 
-__global__ void sum_chunks_kernel(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks) {
+__global__ void sum_chunks_kernel(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, bool accumulate) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pixels) return;
     float4 s = partials[i];
+    if (accumulate) { const float4 p = accum[i]; s.x = p.x + s.x; s.y = p.y + s.y; s.z = p.z + s.z; s.w = p.w + s.w; }
     for (uint32_t c = 1; c < n_chunks; ++c) {  // chunk order == sample order
         const float4 p = partials[(size_t)c * n_pixels + i];
         s.x = s.x + p.x; s.y = s.y + p.y; s.z = s.z + p.z; s.w = s.w + p.w;
@@ -194,6 +197,16 @@ __global__ void resolve_kernel(const float4* accum, uchar4* rgba, uint32_t n_pix
     const float4 c = accum[i];
     const float r = sqrtf(c.x / spp), g = sqrtf(c.y / spp), b = sqrtf(c.z / spp);
     rgba[i] = make_uchar4(f32_as_u8(r * 255.0f), f32_as_u8(g * 255.0f), f32_as_u8(b * 255.0f), 255);
+}
+
+// SkyMap.image (backgrounds.rs:59-81: RGB f32, alpha dropped) -> float4 texels, one 128-bit fetch per lookup
+__global__ void expand_env_kernel(const float* rgb, float4* out, size_t n) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = make_float4(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2], 0.0f);
+}
+cudaError_t launch_expand_env(const float* rgb, float4* out, size_t n, cudaStream_t st) {
+    expand_env_kernel<<<1184, 256, 0, st>>>(rgb, out, n);
+    return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------ batch (parity) kernels
@@ -308,8 +321,8 @@ cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bo
     return cudaGetLastError();
 }
 
-cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, cudaStream_t st) {
-    sum_chunks_kernel<<<(n_pixels + 255) / 256, 256, 0, st>>>(partials, accum, n_pixels, n_chunks);
+cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, bool accumulate, cudaStream_t st) {
+    sum_chunks_kernel<<<(n_pixels + 255) / 256, 256, 0, st>>>(partials, accum, n_pixels, n_chunks, accumulate);
     return cudaGetLastError();
 }
 

@@ -40,6 +40,7 @@ struct RenderArgs {
     uint32_t tiles_x, n_tiles;   // 8x4-pixel warp tiles
     uint32_t n_chunks, chunk_samples;  // sample chunks per tile (1 unless the image is small)
     uint32_t refill_threshold;   // 1..32: refill finished lanes once fewer than this many are still walking
+    uint32_t accumulate;         // RTR_FLAG_ACCUMULATE: add to accum instead of overwriting it
     float4* accum;               // W*H: (sum r, sum g, sum b, samples)
     float4* partials;            // n_chunks * W*H when n_chunks > 1
     uint32_t* work_counter;      // zeroed before launch
@@ -48,7 +49,8 @@ struct RenderArgs {
 
 int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh);
 cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
-cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, cudaStream_t st);
+cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, bool accumulate, cudaStream_t st);
+cudaError_t launch_expand_env(const float* rgb, float4* out, size_t n, cudaStream_t st);
 cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels, float spp, cudaStream_t st);
 cudaError_t launch_trace_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float tmin, uint32_t bvh,
                                bool exhaustive, uint32_t k0, uint32_t k1, rtr_hit* out, unsigned long long* stats,
@@ -91,6 +93,7 @@ struct WfArgs {
     uint32_t wave_samples;              // samples of every pixel in flight per wave
     uint32_t bounce;                    // which [extend, shade] pair this launch is
     uint32_t refill_threshold;          // extend refills idle lanes when fewer lanes than this are walking
+    uint32_t accumulate;                // RTR_FLAG_ACCUMULATE: keep what accum already holds
     WfPaths in, out;
     float4* hit;                        // per slot of `in`: (t, bits(ref), u, v)
     float4* accum;                      // W*H (sum r, sum g, sum b, samples)

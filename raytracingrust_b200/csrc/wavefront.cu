@@ -56,7 +56,7 @@ __device__ __forceinline__ void finish_sample(const WfArgs& a, uint32_t pixel, u
 
 __global__ void wf_begin_kernel(const WfArgs a) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < a.n_pixels) a.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    if (i < a.n_pixels && !a.accumulate) a.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     if (i < WFC_WORDS) a.counters[i] = 0u;
 }
 

@@ -65,6 +65,7 @@ def lib():
     L.rtr_host_mesh_get.restype = C.POINTER(A.MeshS)
     L.rtr_host_mesh_destroy.argtypes = [vp]
     L.rtr_host_mesh_destroy.restype = None
+    L.rtr_write_png.argtypes = [C.c_char_p, vp, u32, u32]
     if L.rtr_abi_version() != A.RTR_ABI_VERSION:
         raise ImportError("librtr_b200.so ABI version mismatch")
     _LIB = L
@@ -128,6 +129,14 @@ class _LoadedScene:
 
 def load_scene_json(path):
     return _LoadedScene(path)
+
+
+def write_png(path, rgba):
+    """Headless stand-in for the window blit of RenderTarget.data (src/main.rs:92-97): RGBA8 (H, W, 4) -> PNG file."""
+    rgba = np.ascontiguousarray(rgba, np.uint8)
+    if rgba.ndim != 3 or rgba.shape[2] != 4:
+        raise ValueError("expected an (H, W, 4) uint8 image")
+    _check(lib().rtr_write_png(os.fsencode(path), rgba.ctypes.data, rgba.shape[1], rgba.shape[0]))
 
 
 # ---------------------------------------------------------------------- device objects

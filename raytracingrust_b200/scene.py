@@ -235,6 +235,11 @@ class RenderTarget:
     def image(self):
         return self.data.reshape(self.height, self.width, 4)
 
+    def save_png(self, path):
+        """Headless replacement of the window blit (src/main.rs:92-97)."""
+        from .render import write_png
+        write_png(path, self.image())
+
 
 # ------------------------------------------------------------------ scene
 class LoweredScene:

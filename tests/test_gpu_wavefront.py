@@ -116,3 +116,28 @@ def test_auto_kernel_choice(ctx):
     flat = _scenes.benchmark()  # ships enable_bvh_tree = false
     flat.settings.samples_per_pixel = 2
     assert ctx.upload(flat).render(rt.make_params(flat, 1024, 768, seed=1))[2]["kernel_used"] == A.KERNEL_MEGAKERNEL
+
+
+def test_progressive_accumulation(ctx):
+    """RTR_FLAG_ACCUMULATE: sample slices added into one device buffer (the GUI's continuous mode, src/gui.rs:333-337).
+    The wavefront adds sample by sample, so slices reproduce the one-shot render bit for bit."""
+    import torch
+    scene = _scenes.simple()
+    scene.settings.samples_per_pixel = 9
+    W, H = 1024, 768
+    ds = ctx.upload(scene)
+    acc = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()  # the library launches on its own stream
+    for kernel, exact in ((A.KERNEL_WAVEFRONT, True), (A.KERNEL_MEGAKERNEL, False)):
+        full = ds.render(rt.make_params(scene, W, H, seed=3, kernel=kernel), want_accum=True)[1]
+        for i, (b, c) in enumerate(((0, 4), (4, 3), (7, 2))):
+            p = rt.make_params(scene, W, H, seed=3, kernel=kernel, sample_begin=b, sample_count=c,
+                               flags=A.FLAG_ACCUMULATE if i else 0)
+            ds.render_accumulate_device(p, acc.data_ptr(), want_stats=False)
+        ctx.synchronize()
+        got = acc.cpu().numpy()
+        assert np.all(got[..., 3] == 9)
+        if exact:
+            assert np.array_equal(got, full)
+        else:
+            np.testing.assert_allclose(got, full, rtol=2e-6, atol=1e-6)

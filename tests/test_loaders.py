@@ -148,3 +148,21 @@ def test_obj_loader_on_reference_assets_matches_fixtures():
         pos, nrm, idx = rt.load_obj(path)
         fp, fn, fi = mesh_fixture(name)
         assert np.array_equal(pos, fp) and np.array_equal(nrm, fn) and np.array_equal(idx, fi), name
+
+
+def test_write_png_round_trip(tmp_path):
+    """Headless output (replaces the window blit of RenderTarget.data): PNG written by the host library decodes back."""
+    import cv2
+    rng = np.random.default_rng(5)
+    img = rng.integers(0, 256, (37, 53, 4), dtype=np.uint8)
+    path = str(tmp_path / "out.png")
+    rt.write_png(path, img)
+    back = cv2.imread(path, cv2.IMREAD_UNCHANGED)  # BGRA
+    assert back is not None and back.shape == img.shape
+    assert np.array_equal(back[..., [2, 1, 0, 3]], img)
+    target = rt.RenderTarget(8, 4)
+    target.data[:] = 200
+    target.save_png(path)
+    assert np.all(cv2.imread(path, cv2.IMREAD_UNCHANGED) == 200)
+    with pytest.raises(rt.RtrError):
+        rt.write_png(str(tmp_path / "no_such_dir" / "x.png"), img)
