@@ -108,6 +108,25 @@ def test_reference_facing_render_call(ctx):
     assert np.all(target.image()[..., 3] == 255)
 
 
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("name", ["mesh_hdri", "volumes"])
+def test_converged_image_statistical_parity_meshes(ctx, name):
+    """The same level-3 check on the mesh + HDRI and the volume scenes (independent seeds, >= 4096 spp), through the
+    kernel RTR_KERNEL_AUTO would pick at full size (wavefront) and the megakernel."""
+    scene = _scenes.mesh_hdri(256, 128) if name == "mesh_hdri" else _scenes.volumes(128, 64)
+    scene.settings.samples_per_pixel = 4096
+    W, H = 40, 24
+    acc_o = orc.OracleScene(scene).render(rt.make_params(scene, W, H, seed=99), want_rgba=False)[1][..., :3] / 4096
+    lum = lambda a: float((a * np.array([0.2126, 0.7152, 0.0722], np.float32)).sum(-1).mean())
+    ds = ctx.upload(scene)
+    for kernel in (A.KERNEL_WAVEFRONT, A.KERNEL_MEGAKERNEL):
+        acc_d = ds.render(rt.make_params(scene, W, H, seed=7, kernel=kernel), want_accum=True)[1][..., :3] / 4096
+        # radiance under an HDRI with bright emitters is heavy-tailed even with clamp_indirect = 10: compare relative to the mean
+        rel_rmse = float(np.sqrt(np.mean((acc_d - acc_o) ** 2))) / max(float(acc_o.mean()), 1e-6)
+        assert rel_rmse < 0.06, (name, kernel, rel_rmse)  # two independent CPU seeds differ by 0.025-0.034
+        assert abs(lum(acc_d) - lum(acc_o)) < 0.006 * lum(acc_o), (name, kernel)  # CPU vs CPU: 0.0015
+
+
 @pytest.mark.timeout(600)
 def test_converged_image_statistical_parity(ctx):
     """north_star level 3: >= 4096 spp images agree with an INDEPENDENTLY seeded CPU render within a stated
