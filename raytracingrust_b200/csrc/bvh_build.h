@@ -1,0 +1,33 @@
+// bvh_build.h — device BVH build for sphere scenes (bvh_build.cu)
+#ifndef RTR_BVH_BUILD_H_
+#define RTR_BVH_BUILD_H_
+
+#include <cuda_runtime_api.h>
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../include/rtr.h"
+#include "flat.h"
+
+namespace rtr {
+
+struct DeviceBvh {
+    F4* nodes = nullptr;        // n nodes of 64 B (n-1 Splits in pre-order + the root's pseudo parent)
+    F4* spheres = nullptr;      // n slots in DFS leaf order
+    PrimInfo* sphere_info = nullptr;
+    ObjectRec* objects = nullptr;
+    uint32_t n_nodes = 0, root_entry = 0xFFFFFFFFu, max_depth = 0;
+    uint64_t device_bytes = 0, h2d_bytes = 0;
+    bool nan_centroid = false;
+};
+
+// true when every object of the scene is a Sphere (the case the device builder covers)
+bool device_build_applies(const rtr_scene_desc& d);
+
+// Builds the reference tree (bvh.rs:59-144) for Scene.objects on `st`.  The four result arrays are cudaMalloc'ed
+// and appended to `allocs` (owned by the caller); scratch is freed before returning.  Synchronises `st`.
+cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, DeviceBvh* out, std::vector<void*>& allocs);
+
+}  // namespace rtr
+#endif

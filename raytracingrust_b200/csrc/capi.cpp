@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "../../include/rtr.h"
+#include "bvh_build.h"
 #include "host_flatten.h"
 #include "kernels.h"
 
@@ -53,6 +54,7 @@ struct rtr_scene {
     double build_ms = 0.0;
     uint32_t n_nodes = 0, max_depth = 0;
     uint32_t root_entry_reference = 0xFFFFFFFFu;
+    bool built_on_device = false;
 };
 
 static rtr_status fail(rtr_context* ctx, rtr_status st, const std::string& msg) {
@@ -209,11 +211,23 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     *out = nullptr;
     CU(cudaSetDevice(ctx->device));
     auto t0 = std::chrono::steady_clock::now();
+    // Sphere scenes can have their BVH built on the device (bvh_build.cu): RTR_BVH_BUILD = host | device | auto
+    // (auto: from 4096 objects up, where the level-by-level launches beat the host's recursive sort).
+    bool on_device = false;
+    {
+        const char* mode = std::getenv("RTR_BVH_BUILD");
+        const bool applies = device_build_applies(*desc);
+        if (mode && std::strcmp(mode, "device") == 0) on_device = applies;
+        else if (mode && std::strcmp(mode, "host") == 0) on_device = false;
+        else on_device = applies && desc->n_objects >= 4096;
+    }
+    rtr_scene_desc host_desc = *desc;
+    if (on_device) { host_desc.objects = nullptr; host_desc.n_objects = 0; }  // materials / background still flatten on the host
     HostFlat flat;
     std::string err;
     int rc = RTR_OK;
     try {
-        rc = flatten_scene(*desc, flat, err);
+        rc = flatten_scene(host_desc, flat, err);
     } catch (const std::bad_alloc&) {
         return fail(ctx, RTR_OOM, "host allocation failed while flattening");
     }
@@ -275,6 +289,20 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     v.linear_needs_inv = 0;
     for (const ObjectRec& o : flat.objects)
         if (RTR_REF_KIND(o.entry) != REF_SPHERE && RTR_REF_KIND(o.entry) != REF_EMPTY) v.linear_needs_inv = 1;
+    if (on_device) {
+        DeviceBvh bvh;
+        cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, &bvh, s->allocs);
+        if (be != cudaSuccess) { rtr_scene_destroy(s); return cuda_fail(ctx, be, "device BVH build"); }
+        if (bvh.nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
+        if (bvh.max_depth + 2 > 48) { rtr_scene_destroy(s); return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack"); }
+        v.nodes = bvh.nodes; v.spheres = bvh.spheres; v.sphere_info = bvh.sphere_info; v.objects = bvh.objects;
+        v.root_entry = bvh.root_entry; s->root_entry_reference = bvh.root_entry;
+        v.n_objects = desc->n_objects; v.n_nodes = bvh.n_nodes; v.n_sphere_slots = desc->n_objects;
+        s->n_nodes = bvh.n_nodes; s->max_depth = bvh.max_depth;
+        s->device_bytes += bvh.device_bytes; s->h2d_bytes += bvh.h2d_bytes;
+        s->built_on_device = true;
+    }
+    s->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
     return RTR_OK;
 }

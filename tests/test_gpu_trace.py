@@ -1,5 +1,7 @@
 """Parity level 1 — closest hit for fixed ray batches: rtr_trace_batch vs the oracle's reference-shaped
 (unculled, both-children) walk.  IDs exact, t/point/normal bit-identical."""
+import os
+
 import numpy as np
 import pytest
 
@@ -129,6 +131,11 @@ def test_full_size_culled_equals_exhaustive_1m_spheres(ctx):
     primary = ctx.camera_rays(p, pix, np.zeros_like(pix))
     h = ds.trace_batch(primary)
     hx = ds.trace_batch(primary, flags=A.FLAG_EXHAUSTIVE)
+    os.environ["RTR_BVH_BUILD"] = "host"  # the default above was the device build: the host rebuild must agree
+    try:
+        assert np.array_equal(h, ctx.upload(scene).trace_batch(primary))
+    finally:
+        os.environ.pop("RTR_BVH_BUILD")
     assert np.array_equal(h, hx)
     # ... and the gate-box traversal tree returns exactly what a walk of the reference's own topology returns
     assert np.array_equal(h, ds.trace_batch(primary, flags=A.FLAG_REFERENCE_TREE))
