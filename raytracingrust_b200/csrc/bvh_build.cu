@@ -128,7 +128,7 @@ __global__ void k_advance(BuildArrays a, uint32_t depth) {
 }
 
 // leaves in DFS order: slot = position, rank = position (bvh.rs:183-187 tie rule)
-__global__ void k_emit_leaves(BuildArrays a, F4* spheres, PrimInfo* info, ObjectRec* objects) {
+__global__ void k_emit_leaves(BuildArrays a, F4* spheres, PrimInfo* info, ObjectRec* objects, F4* linear) {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= a.n) return;
     const uint32_t h = a.perm[p];
@@ -141,6 +141,7 @@ __global__ void k_emit_leaves(BuildArrays a, F4* spheres, PrimInfo* info, Object
     o.entry = o.entry_reference = RTR_MAKE_REF(REF_SPHERE, p);
     o._pad[0] = o._pad[1] = 0u;
     objects[h] = o;
+    linear[h] = F4{s.x, s.y, s.z, s.w};
 }
 
 __device__ __forceinline__ void child_box(const BuildArrays& a, uint32_t lo, uint32_t hi, uint32_t node, float4& mn, float4& mx) {
@@ -243,6 +244,7 @@ cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t s
     out->spheres = (F4*)alloc(n * sizeof(F4), true);
     out->sphere_info = (PrimInfo*)alloc(n * sizeof(PrimInfo), true);
     out->objects = (ObjectRec*)alloc(n * sizeof(ObjectRec), true);
+    out->linear_spheres = (F4*)alloc(n * sizeof(F4), true);
     // one sort plan for every level: 64-bit keys, the bits above (32 + bits(n)) are zero
     int end_bit = 32;
     while (end_bit < 64 && (1ull << (end_bit - 32)) < n) ++end_bit;
@@ -275,7 +277,7 @@ cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t s
         k_advance<<<grid, 256, 0, st>>>(a, L);
         step(cudaGetLastError());
     }
-    k_emit_leaves<<<grid, 256, 0, st>>>(a, out->spheres, out->sphere_info, out->objects);
+    k_emit_leaves<<<grid, 256, 0, st>>>(a, out->spheres, out->sphere_info, out->objects, out->linear_spheres);
     for (uint32_t L = levels; L-- > 0 && e == cudaSuccess;) k_node_boxes<<<grid, 256, 0, st>>>(a, L);
     k_emit_nodes<<<grid, 256, 0, st>>>(a, out->nodes);
     step(cudaGetLastError());

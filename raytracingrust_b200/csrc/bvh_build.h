@@ -17,6 +17,7 @@ struct DeviceBvh {
     F4* spheres = nullptr;      // n slots in DFS leaf order
     PrimInfo* sphere_info = nullptr;
     ObjectRec* objects = nullptr;
+    F4* linear_spheres = nullptr;  // the spheres in Scene.objects order (BVH-off scan)
     uint32_t n_nodes = 0, root_entry = 0xFFFFFFFFu, max_depth = 0;
     uint64_t device_bytes = 0, h2d_bytes = 0;
     bool nan_centroid = false;

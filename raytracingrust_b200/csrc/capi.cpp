@@ -212,14 +212,14 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     CU(cudaSetDevice(ctx->device));
     auto t0 = std::chrono::steady_clock::now();
     // Sphere scenes can have their BVH built on the device (bvh_build.cu): RTR_BVH_BUILD = host | device | auto
-    // (auto: from 4096 objects up, where the level-by-level launches beat the host's recursive sort).
+    // (auto: from 2048 objects up, where the level-by-level launches beat the host's recursive sort).
     bool on_device = false;
     {
         const char* mode = std::getenv("RTR_BVH_BUILD");
         const bool applies = device_build_applies(*desc);
         if (mode && std::strcmp(mode, "device") == 0) on_device = applies;
         else if (mode && std::strcmp(mode, "host") == 0) on_device = false;
-        else on_device = applies && desc->n_objects >= 4096;
+        else on_device = applies && desc->n_objects >= 2048;
     }
     rtr_scene_desc host_desc = *desc;
     if (on_device) { host_desc.objects = nullptr; host_desc.n_objects = 0; }  // materials / background still flatten on the host
@@ -289,6 +289,17 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     v.linear_needs_inv = 0;
     for (const ObjectRec& o : flat.objects)
         if (RTR_REF_KIND(o.entry) != REF_SPHERE && RTR_REF_KIND(o.entry) != REF_EMPTY) v.linear_needs_inv = 1;
+    if (!on_device && v.n_objects > 0) {  // all-sphere scene: object-order sphere records for the BVH-off scan
+        bool all_spheres = true;
+        for (const ObjectRec& o : flat.objects) all_spheres = all_spheres && RTR_REF_KIND(o.entry) == REF_SPHERE;
+        if (all_spheres) {
+            std::vector<F4> lin(flat.objects.size());
+            for (size_t i = 0; i < lin.size(); ++i) lin[i] = flat.spheres[RTR_REF_INDEX(flat.objects[i].entry)];
+            cudaError_t le = upload(s, lin, &v.linear_spheres, ctx->stream);
+            if (le == cudaSuccess) le = cudaStreamSynchronize(ctx->stream);
+            if (le != cudaSuccess) { rtr_scene_destroy(s); return cuda_fail(ctx, le, "rtr_scene_upload"); }
+        }
+    }
     if (on_device) {
         DeviceBvh bvh;
         cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, &bvh, s->allocs);
@@ -296,6 +307,7 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
         if (bvh.nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
         if (bvh.max_depth + 2 > 48) { rtr_scene_destroy(s); return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack"); }
         v.nodes = bvh.nodes; v.spheres = bvh.spheres; v.sphere_info = bvh.sphere_info; v.objects = bvh.objects;
+        v.linear_spheres = bvh.linear_spheres;
         v.root_entry = bvh.root_entry; s->root_entry_reference = bvh.root_entry;
         v.n_objects = desc->n_objects; v.n_nodes = bvh.n_nodes; v.n_sphere_slots = desc->n_objects;
         s->n_nodes = bvh.n_nodes; s->max_depth = bvh.max_depth;

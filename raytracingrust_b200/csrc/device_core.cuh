@@ -404,6 +404,16 @@ __device__ __forceinline__ LiteHit world_hit(const SceneView& sc, bool bvh, cons
         return best;
     }
     float closest = RTR_INF;  // closest_so_far (scene.rs:144)
+    if (sc.linear_spheres != nullptr) {  // all spheres: same scan, same order, without the per-object dispatch
+        uint32_t winner = 0xFFFFFFFFu;
+        for (uint32_t i = 0; i < sc.n_objects; ++i) {
+            float t;
+            if (COUNT) cnt->spheres++;
+            if (sphere_t(ldg4(sc.linear_spheres + i), r, tmin, closest, t)) { closest = t; winner = i; }
+        }
+        if (winner != 0xFFFFFFFFu) { best.t = closest; best.ref = sc.objects[winner].entry; }
+        return best;
+    }
     for (uint32_t i = 0; i < sc.n_objects; ++i) {
         const uint32_t entry = sc.reference_tree ? sc.objects[i].entry_reference : sc.objects[i].entry;
         const uint32_t kind = RTR_REF_KIND(entry);

@@ -90,6 +90,8 @@ struct SceneView {
     const ObjectRec* objects;
     const MaterialRec* materials;
     const F4* env;            // SkyMap texels as float4 (rgb, 0)
+    const F4* linear_spheres; // Scene.objects order copy of the spheres when EVERY object is a sphere (else null):
+                              // the BVH-off scan (scene.rs:141-156) then reads consecutive records, no dispatch
     BackgroundRec background;
     uint32_t root_entry;      // entry ref of the scene tree being walked (traversal tree, or the reference topology)
     uint32_t reference_tree;  // 1: walk the reference topology (leaf slots carry no box) — counting / validation
