@@ -261,6 +261,22 @@ void rtr_host_mesh_destroy(rtr_host_mesh* hm);
 /* ---- headless output (replaces the window blit of RenderTarget.data, src/main.rs:92-97) ---- */
 /* 8-bit RGBA PNG of a host RGBA8 buffer as rtr_render fills it */
 rtr_status rtr_write_png(const char* path, const uint8_t* rgba8, uint32_t width, uint32_t height);
+/* fp32 image (the accumulation buffer divided by spp, or any RGB/RGBA float image) as a scan-line OpenEXR file with
+ * float channels and ZIP blocks; channels = 3 (RGB) or 4 (RGBA), interleaved, row 0 = top */
+rtr_status rtr_write_exr(const char* path, const float* pixels, uint32_t width, uint32_t height,
+                         uint32_t channels);
+
+/* ---- environment maps: SkyMap::new (backgrounds.rs:58-80) ---- */
+typedef struct rtr_host_image rtr_host_image;
+/* First RGB(A) layer of a single-part scan-line OpenEXR file (half / float / uint channels; NONE, RLE, ZIPS, ZIP,
+ * PIZ or PXR24 blocks), or a Radiance RGBE .hdr file.  Texels come back as the reference stores them: RGB f32,
+ * image[x + y*width], row 0 = first row of the data window; pass them as rtr_background.texels.
+ * RTR_UNSUPPORTED for tiled / multi-part / deep files and B44 / DWA blocks, message via rtr_last_error(NULL). */
+rtr_status rtr_image_load(const char* path, rtr_host_image** out);
+uint32_t rtr_host_image_width(const rtr_host_image* img);
+uint32_t rtr_host_image_height(const rtr_host_image* img);
+const float* rtr_host_image_rgb(const rtr_host_image* img);
+void rtr_host_image_destroy(rtr_host_image* img);
 
 #ifdef __cplusplus
 }

@@ -140,5 +140,6 @@ EXPORTED_SYMBOLS = [
     "rtr_trace_batch", "rtr_scatter_batch", "rtr_background_batch", "rtr_camera_rays",
     "rtr_scene_load_json", "rtr_host_scene_desc", "rtr_host_scene_camera", "rtr_host_scene_settings",
     "rtr_host_scene_destroy", "rtr_mesh_load_obj", "rtr_host_mesh_get", "rtr_host_mesh_destroy",
-    "rtr_write_png",
+    "rtr_write_png", "rtr_write_exr", "rtr_image_load", "rtr_host_image_width", "rtr_host_image_height",
+    "rtr_host_image_rgb", "rtr_host_image_destroy",
 ]

@@ -293,8 +293,9 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
 }
 
 // [bucket:leaf_step]
+// the primitive test of a leaf step, without the pop: `cur` is read only
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED, typename STACK>
-__device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
+__device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cur, const int sp, LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
                                           Counters* cnt) {
     const uint32_t kind = RTR_REF_KIND(cur);
@@ -333,6 +334,12 @@ __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, in
         float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack.nested(sp), EXHAUSTIVE, COUNT ? cnt : nullptr);
         if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
     }
+}
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED, typename STACK>
+__device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
+                                          const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
+                                          Counters* cnt) {
+    leaf_test<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
     cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
 }
 

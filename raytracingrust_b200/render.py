@@ -66,6 +66,16 @@ def lib():
     L.rtr_host_mesh_destroy.argtypes = [vp]
     L.rtr_host_mesh_destroy.restype = None
     L.rtr_write_png.argtypes = [C.c_char_p, vp, u32, u32]
+    L.rtr_write_exr.argtypes = [C.c_char_p, vp, u32, u32, u32]
+    L.rtr_image_load.argtypes = [C.c_char_p, C.POINTER(vp)]
+    L.rtr_host_image_width.argtypes = [vp]
+    L.rtr_host_image_width.restype = u32
+    L.rtr_host_image_height.argtypes = [vp]
+    L.rtr_host_image_height.restype = u32
+    L.rtr_host_image_rgb.argtypes = [vp]
+    L.rtr_host_image_rgb.restype = C.POINTER(C.c_float)
+    L.rtr_host_image_destroy.argtypes = [vp]
+    L.rtr_host_image_destroy.restype = None
     if L.rtr_abi_version() != A.RTR_ABI_VERSION:
         raise ImportError("librtr_b200.so ABI version mismatch")
     _LIB = L
@@ -137,6 +147,26 @@ def write_png(path, rgba):
     if rgba.ndim != 3 or rgba.shape[2] != 4:
         raise ValueError("expected an (H, W, 4) uint8 image")
     _check(lib().rtr_write_png(os.fsencode(path), rgba.ctypes.data, rgba.shape[1], rgba.shape[0]))
+
+
+def write_exr(path, image):
+    """fp32 (H, W, 3|4) image -> scan-line OpenEXR, float channels, ZIP blocks (rtr_write_exr)."""
+    image = np.ascontiguousarray(image, np.float32)
+    if image.ndim != 3 or image.shape[2] not in (3, 4):
+        raise ValueError("expected an (H, W, 3) or (H, W, 4) float image")
+    _check(lib().rtr_write_exr(os.fsencode(path), image.ctypes.data, image.shape[1], image.shape[0], image.shape[2]))
+
+
+def load_image(path):
+    """SkyMap::new's file read (backgrounds.rs:59-73): OpenEXR or Radiance HDR -> (H, W, 3) float32, row 0 = top."""
+    h = C.c_void_p()
+    _check(lib().rtr_image_load(os.fsencode(path), C.byref(h)))
+    try:
+        L = lib()
+        W, H = L.rtr_host_image_width(h), L.rtr_host_image_height(h)
+        return np.ctypeslib.as_array(L.rtr_host_image_rgb(h), shape=(H, W, 3)).copy()
+    finally:
+        lib().rtr_host_image_destroy(h)
 
 
 # ---------------------------------------------------------------------- device objects

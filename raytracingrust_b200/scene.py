@@ -212,13 +212,11 @@ class SkyMap(Background):
 
 
 def _read_exr(path):
-    import os
-    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
-    import cv2
-    img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
-    if img is None:
-        raise IOError("could not read image!")  # .expect (backgrounds.rs:72)
-    return img[:, :, 2::-1].astype(np.float32)  # BGR -> RGB, alpha dropped
+    from .render import load_image  # the host library's own OpenEXR / Radiance reader (rtr_image_load)
+    try:
+        return load_image(path)
+    except Exception as e:
+        raise IOError(f"could not read image! ({e})")  # .expect (backgrounds.rs:72)
 
 
 # ------------------------------------------------------------------ render target
