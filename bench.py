@@ -28,6 +28,7 @@ import numpy as np  # noqa: E402
 WORKLOADS = {
     # name: (scene recipe, W, H, spp, description)
     "benchmark": ("benchmark", 1920, 1080, 1024, "scenes/benchmark.json 1920x1080x1024spp (5 spheres, BVH off as shipped)"),
+    "benchmark_bvh": ("benchmark_bvh", 1920, 1080, 1024, "scenes/benchmark.json with enable_bvh_tree forced on, 1920x1080x1024spp (SURVEY C2: both settings reported)"),
     "simple": ("simple", 1920, 1080, 1024, "scenes/simple.json 1920x1080x1024spp (102 spheres, BVH on)"),
     "mesh_hdri": ("mesh_hdri", 1920, 1080, 256, "house+plane+fancy_monkey meshes, synthetic 4096x2048 HDRI, 1920x1080x256spp"),
     "volumes": ("volumes", 1920, 1080, 64, "mesh/sphere-bounded media over plane, synthetic HDRI, 1920x1080x64spp"),
@@ -43,6 +44,10 @@ def make_scene(name):
         return _scenes.volumes(2048, 1024)
     if name == "bvh_stress":
         return _scenes.random_spheres(1_000_000)
+    if name == "benchmark_bvh":
+        s = _scenes.benchmark()
+        s.settings.enable_bvh_tree = True
+        return s
     return getattr(_scenes, name)()
 
 
