@@ -23,7 +23,7 @@ namespace rtr {
 enum { ST_FRESH = 0, ST_LAUNCH = 1, ST_SHADE = 2, ST_DEAD = 3 };
 
 template <bool EXHAUSTIVE, bool COUNT, bool BVH>
-__global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_MEGA_MIN_BLOCKS) render_megakernel(const RenderArgs a) {
+__global__ void __launch_bounds__(RTR_MEGA_THREADS, BVH ? RTR_MEGA_MIN_BLOCKS : RTR_MEGA_MIN_BLOCKS_SCAN) render_megakernel(const RenderArgs a) {
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
     __shared__ uint2 short_stack[BVH ? RTR_SHORT_STACK : 1][RTR_MEGA_THREADS];
     ShortStack<RTR_SHORT_STACK, RTR_MEGA_THREADS> wstack;

@@ -16,6 +16,10 @@ namespace rtr {
 #define RTR_MEGA_MIN_BLOCKS 7  // resident CTAs per SM the register allocation must allow (swept on B200: 4..8)
 #endif
 
+#ifndef RTR_MEGA_MIN_BLOCKS_SCAN
+#define RTR_MEGA_MIN_BLOCKS_SCAN 7  // the same for the BVH-off instantiations (linear scan, no traversal state)
+#endif
+
 #ifndef RTR_SHORT_STACK
 #define RTR_SHORT_STACK 8  // traversal-stack entries per thread kept in shared memory (deeper ones spill to local memory)
 #endif
