@@ -104,7 +104,9 @@ class ClockSampler(threading.Thread):
 
 # bounded CPU sample per workload (W, H, spp factor): the reference-shaped CPU walk tests every pierced subtree, which
 # on the 1 M-sphere scene is ~150x slower per ray than on the others — keep each sample to seconds of CPU work
-CPU_SAMPLE = {"bvh_stress": (256, 256, 1 / 16.0)}
+# (16 host cores: benchmark ~6 s, simple ~4 s, mesh_hdri ~5 s, volumes ~9 s, bvh_stress ~1 s per sample)
+CPU_SAMPLE = {"bvh_stress": (256, 256, 1 / 16.0), "benchmark": (1920, 1080, 16.0), "benchmark_bvh": (1920, 1080, 16.0),
+              "simple": (1920, 1080, 4.0)}
 
 
 def cpu_sample_for(workload, W, H, spp_sample):
