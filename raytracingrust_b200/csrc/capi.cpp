@@ -40,6 +40,7 @@ struct rtr_context {
     uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
     uint64_t wf_target_paths = 1ull << 23;  // RTR_WF_PATHS: paths in flight per wave
     int wf_use_graph = 1;  // RTR_WF_GRAPH
+    int use_scan_kernel = 1;  // RTR_SCAN_KERNEL: 0 sends all-sphere BVH-off renders through the generic megakernel
     char* batch_in = nullptr; size_t batch_in_bytes = 0;
     char* batch_in2 = nullptr; size_t batch_in2_bytes = 0;
     char* batch_out = nullptr; size_t batch_out_bytes = 0;
@@ -156,6 +157,7 @@ rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
         if (v >= 1024) ctx->wf_target_paths = (uint64_t)v;
     }
     if (const char* e = std::getenv("RTR_WF_GRAPH")) ctx->wf_use_graph = std::atoi(e);
+    if (const char* e = std::getenv("RTR_SCAN_KERNEL")) ctx->use_scan_kernel = std::atoi(e);
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->wf_counters, WFC_WORDS * sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->stats, STAT_COUNT * sizeof(unsigned long long)));
@@ -505,7 +507,11 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     a.tiles_x = (W + 7) / 8;
     a.n_tiles = a.tiles_x * ((H + 3) / 4);
     // persistent grid: one block per resident slot
-    int per_sm = megakernel_max_blocks_per_sm(exhaustive, count_work, p->settings.enable_bvh_tree != 0);
+    // BVH off and every object a sphere (scenes/benchmark.json): the scan kernel (scan.cu), same results
+    const bool scan = ctx->use_scan_kernel != 0 && p->settings.enable_bvh_tree == 0 && a.sc.linear_spheres != nullptr &&
+                      p->settings.max_ray_depth >= 1;
+    int per_sm = scan ? scan_kernel_max_blocks_per_sm(count_work)
+                      : megakernel_max_blocks_per_sm(exhaustive, count_work, p->settings.enable_bvh_tree != 0);
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "megakernel cannot be resident on this device");
     const uint32_t resident_warps = (uint32_t)ctx->sm_count * per_sm * (RTR_MEGA_THREADS / 32);
     // small image + many samples: split the samples of a tile into chunks so the chip is full
@@ -534,7 +540,8 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
         uint32_t blocks = (uint32_t)ctx->sm_count * per_sm;
         uint32_t need_blocks = (items + (RTR_MEGA_THREADS / 32) - 1) / (RTR_MEGA_THREADS / 32);
         if (blocks > need_blocks) blocks = need_blocks;
-        CU(launch_megakernel(a, (int)blocks, exhaustive, count_work, ctx->stream));
+        if (scan) CU(launch_scan_kernel(a, (int)blocks, count_work, ctx->stream));
+        else CU(launch_megakernel(a, (int)blocks, exhaustive, count_work, ctx->stream));
         ++launches;
         if (a.n_chunks > 1) {
             CU(launch_sum_chunks(a.partials, accum_dev, W * H, a.n_chunks, a.accumulate != 0, ctx->stream));

@@ -20,6 +20,10 @@ namespace rtr {
 #define RTR_MEGA_MIN_BLOCKS_SCAN 7  // the same for the BVH-off instantiations (linear scan, no traversal state)
 #endif
 
+#ifndef RTR_SCAN_MIN_BLOCKS
+#define RTR_SCAN_MIN_BLOCKS 8  // resident CTAs per SM of the all-sphere scan kernel (scan.cu)
+#endif
+
 #ifndef RTR_SHORT_STACK
 #define RTR_SHORT_STACK 8  // traversal-stack entries per thread kept in shared memory (deeper ones spill to local memory)
 #endif
@@ -53,6 +57,9 @@ struct RenderArgs {
 
 int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh);
 cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
+// scan.cu: BVH off + every object a sphere (scenes/benchmark.json); same RenderArgs, same results as the megakernel
+int scan_kernel_max_blocks_per_sm(bool count);
+cudaError_t launch_scan_kernel(const RenderArgs& a, int grid, bool count, cudaStream_t st);
 cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, bool accumulate, cudaStream_t st);
 cudaError_t launch_expand_env(const float* rgb, float4* out, size_t n, cudaStream_t st);
 cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels, float spp, cudaStream_t st);
