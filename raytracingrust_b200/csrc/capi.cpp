@@ -421,7 +421,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     a.accum = accum_dev;
     a.counters = ctx->wf_counters;
     a.stats = ctx->stats;
-    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work);
+    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u);
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
     auto blocks_for = [&](uint64_t items, int cap_per_sm) {
         uint64_t b = (items + RTR_WF_THREADS - 1) / RTR_WF_THREADS;
@@ -503,6 +503,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     a.enable_bvh_tree = p->settings.enable_bvh_tree;
     a.mode = p->settings.mode;
     a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
+    for (uint32_t i = 0; i < 10; ++i) { a.rk0[i] = a.k0 + i * 0x9E3779B9u; a.rk1[i] = a.k1 + i * 0xBB67AE85u; }
     a.sample_begin = p->sample_begin; a.sample_count = count;
     a.tiles_x = (W + 7) / 8;
     a.n_tiles = a.tiles_x * ((H + 3) / 4);
@@ -511,7 +512,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     const bool scan = ctx->use_scan_kernel != 0 && p->settings.enable_bvh_tree == 0 && a.sc.linear_spheres != nullptr &&
                       p->settings.max_ray_depth >= 1;
     int per_sm = scan ? scan_kernel_max_blocks_per_sm(count_work)
-                      : megakernel_max_blocks_per_sm(exhaustive, count_work, p->settings.enable_bvh_tree != 0);
+                      : megakernel_max_blocks_per_sm(exhaustive, count_work, p->settings.enable_bvh_tree != 0, a.sc.n_volumes != 0u);
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "megakernel cannot be resident on this device");
     const uint32_t resident_warps = (uint32_t)ctx->sm_count * per_sm * (RTR_MEGA_THREADS / 32);
     // small image + many samples: split the samples of a tile into chunks so the chip is full

@@ -135,18 +135,53 @@ __device__ __forceinline__ bool slab(const float4& mn, const float4& mx, const R
 }
 
 // ------------------------------------------------------------------ primitives  [bucket:primitive_tests]
-// Sphere::hit (objects.rs:23-50), t only; point/normal are rebuilt for the winner in finish_hit
+// Sphere::hit (objects.rs:23-50), t only; point/normal are rebuilt for the winner in finish_hit.
+// Three shortcuts keep the reference's result bit for bit while skipping its IEEE sqrt / divisions (each ~10 SASS
+// instructions, and a ~45-instruction slow path whenever the numerator is exactly 0 — ncu on benchmark.json: 7 % of all
+// warp-instructions, because a ray leaving the r=100 ground sphere has c == 0 exactly, so -half_b -/+ sqrtd == 0):
+//  (1) origin outside and moving away (c > 0, half_b > 0): fl(a*c) >= 0 so disc <= fl(half_b^2) and, sqrt being
+//      monotonic with sqrt(fl(x^2)) == |x|, sqrtd <= half_b: both numerators are <= 0, both roots <= 0 < tmin -> miss;
+//  (2) origin inside (c < 0): disc >= fl(half_b^2), sqrtd >= |half_b|, the first numerator is <= 0 -> the first
+//      root fails `root < tmin` without being computed;
+//  (3) a zero numerator over a > 0 is that same signed zero.
+// All three need tmin > 0, a > 0, a non-NaN discriminant and half_b^2 neither overflowed nor denormal (the
+// sqrt(fl(x^2)) == |x| identity); otherwise the plain sequence runs (tests/test_sphere_shortcuts.py sweeps both forms).
+// SHORTCUTS is on in the linear scan (scan.cu: +3.2 % on benchmark.json, where rays leaving the ground sphere meet
+// cases 1-3 at every bounce) and off in the BVH walks, whose candidates have already passed a box test: there the
+// extra compares and branches cost 4 % (simple.json, 1 M spheres; same-box A/B).
+template <bool SHORTCUTS>
+__device__ __forceinline__ float div_or_zero(float num, float a) {
+    if (!SHORTCUTS) return num / a;
+    float q = num;
+    if (!(num == 0.0f && a > 0.0f)) {
+        // the volatile move pins the division inside this branch: written as a select, nvcc divides
+        // unconditionally (FCHK + slow-path call included) and picks the result afterwards
+        float n;
+        asm volatile("mov.f32 %0, %1;" : "=f"(n) : "f"(num));
+        q = n / a;
+    }
+    return q;
+}
+template <bool SHORTCUTS = false>
 __device__ __forceinline__ bool sphere_t(const float4& s, const Ray& r, float tmin, float tmax, float& t) {
     v3 oc = r.o - xyz(s);
     float a = dot(r.d, r.d);
     float half_b = dot(oc, r.d);
     float c = dot(oc, oc) - s.w * s.w;
-    float disc = half_b * half_b - a * c;
+    float hb2 = half_b * half_b;
+    float disc = hb2 - a * c;
     if (disc < 0.0f) return false;
+    const bool tame = SHORTCUTS && disc >= 0.0f && a > 0.0f && tmin > 0.0f && hb2 >= 1.17549435e-38f && hb2 < RTR_INF;
+    if (tame && c > 0.0f && half_b > 0.0f) return false;
     float sqrtd = sqrtf(disc);
-    float root = (-half_b - sqrtd) / a;
-    if (root < tmin || tmax < root) {
-        root = (-half_b + sqrtd) / a;
+    bool second = tame && c < 0.0f;
+    float root = 0.0f;
+    if (!second) {
+        root = div_or_zero<SHORTCUTS>(-half_b - sqrtd, a);
+        second = root < tmin || tmax < root;
+    }
+    if (second) {
+        root = div_or_zero<SHORTCUTS>(-half_b + sqrtd, a);
         if (root < tmin || tmax < root) return false;
     }
     t = root;
@@ -294,7 +329,7 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
 
 // [bucket:leaf_step]
 // the primitive test of a leaf step, without the pop: `cur` is read only
-template <bool EXHAUSTIVE, bool COUNT, bool NESTED, typename STACK>
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED, bool VOLUMES = true, typename STACK>
 __device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cur, const int sp, LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
                                           Counters* cnt) {
@@ -329,17 +364,17 @@ __device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cu
         if (COUNT) cnt->spheres += 2;
         if (sphere_t(s0, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i), 0.0f, 0.0f);
         if (sphere_t(s1, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i + 1), 0.0f, 0.0f);
-    } else if (!NESTED && kind == REF_VOLUME) {
+    } else if (VOLUMES && !NESTED && kind == REF_VOLUME) {
         const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
         float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack.nested(sp), EXHAUSTIVE, COUNT ? cnt : nullptr);
         if (t == t) offer(sc, best, t, cur, 0.0f, 0.0f);
     }
 }
-template <bool EXHAUSTIVE, bool COUNT, bool NESTED, typename STACK>
+template <bool EXHAUSTIVE, bool COUNT, bool NESTED, bool VOLUMES = true, typename STACK>
 __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
                                           Counters* cnt) {
-    leaf_test<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
+    leaf_test<EXHAUSTIVE, COUNT, NESTED, VOLUMES>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
     cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
 }
 

@@ -22,7 +22,8 @@ namespace rtr {
 // longest walk of the warp ends (ncu before this: 4.3 of 32 lanes active in the node loop on the mesh scene).
 enum { ST_FRESH = 0, ST_LAUNCH = 1, ST_SHADE = 2, ST_DEAD = 3 };
 
-template <bool EXHAUSTIVE, bool COUNT, bool BVH>
+// VOLUMES = false (BVH walks of scenes without a Volume): Volume::hit, a non-inlined call, is compiled out of the walk.
+template <bool EXHAUSTIVE, bool COUNT, bool BVH, bool VOLUMES>
 __global__ void __launch_bounds__(RTR_MEGA_THREADS, BVH ? RTR_MEGA_MIN_BLOCKS : RTR_MEGA_MIN_BLOCKS_SCAN) render_megakernel(const RenderArgs a) {
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
     __shared__ uint2 short_stack[BVH ? RTR_SHORT_STACK : 1][RTR_MEGA_THREADS];
@@ -141,7 +142,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, BVH ? RTR_MEGA_MIN_BLOCKS : 
                     if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, ray, inv, 0.00001f, RTR_INF, wstack, &cnt);
                 }
                 if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
-                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, ray, inv, 0.00001f, key, wstack, &cnt);
+                    leaf_step<EXHAUSTIVE, COUNT, false, VOLUMES>(a.sc, cur, sp, best, ray, inv, 0.00001f, key, wstack, &cnt);
             } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
             walking = cur != RTR_REF_DONE;
         }
@@ -293,28 +294,26 @@ __global__ void camera_rays_kernel(const CameraBasis cam, uint32_t W, uint32_t H
 
 // ------------------------------------------------------------------ launchers (called from capi.cpp)
 template <typename F>
-static auto pick_megakernel(bool exhaustive, bool count, bool bvh, F f) {
-#define RTR_PICK(E, C, B) return f(render_megakernel<E, C, B>)
-    if (exhaustive) {
-        if (count) { if (bvh) RTR_PICK(true, true, true); else RTR_PICK(true, true, false); }
-        else { if (bvh) RTR_PICK(true, false, true); else RTR_PICK(true, false, false); }
-    } else {
-        if (count) { if (bvh) RTR_PICK(false, true, true); else RTR_PICK(false, true, false); }
-        else { if (bvh) RTR_PICK(false, false, true); else RTR_PICK(false, false, false); }
-    }
+static auto pick_megakernel(bool exhaustive, bool count, bool bvh, bool volumes, F f) {
+#define RTR_PICK(E, C) \
+    do { if (!bvh) return f(render_megakernel<E, C, false, true>); \
+         if (volumes) return f(render_megakernel<E, C, true, true>); \
+         return f(render_megakernel<E, C, true, false>); } while (0)
+    if (exhaustive) { if (count) RTR_PICK(true, true); else RTR_PICK(true, false); }
+    else { if (count) RTR_PICK(false, true); else RTR_PICK(false, false); }
 #undef RTR_PICK
 }
 
-int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh) {
+int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh, bool volumes) {
     int n = 0;
-    cudaError_t e = pick_megakernel(exhaustive, count, bvh, [&](void (*k)(const RenderArgs)) {
+    cudaError_t e = pick_megakernel(exhaustive, count, bvh, volumes, [&](void (*k)(const RenderArgs)) {
         return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_MEGA_THREADS, 0);
     });
     return e == cudaSuccess ? n : 0;
 }
 
 cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st) {
-    pick_megakernel(exhaustive, count, a.enable_bvh_tree != 0, [&](void (*k)(const RenderArgs)) {
+    pick_megakernel(exhaustive, count, a.enable_bvh_tree != 0, a.sc.n_volumes != 0u, [&](void (*k)(const RenderArgs)) {
         k<<<grid, RTR_MEGA_THREADS, 0, st>>>(a);
         return cudaSuccess;
     });

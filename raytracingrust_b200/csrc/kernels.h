@@ -21,7 +21,7 @@ namespace rtr {
 #endif
 
 #ifndef RTR_SCAN_MIN_BLOCKS
-#define RTR_SCAN_MIN_BLOCKS 8  // resident CTAs per SM of the all-sphere scan kernel (scan.cu)
+#define RTR_SCAN_MIN_BLOCKS 7  // resident CTAs per SM of the all-sphere scan kernel (scan.cu)
 #endif
 
 #ifndef RTR_SHORT_STACK
@@ -44,6 +44,7 @@ struct RenderArgs {
     uint32_t enable_bvh_tree;
     uint32_t mode;
     uint32_t k0, k1;             // Philox key = seed
+    uint32_t rk0[10], rk1[10];   // the ten Philox round keys (k + i*W): LOP3 reads them straight from the constant bank
     uint32_t sample_begin, sample_count;
     uint32_t tiles_x, n_tiles;   // 8x4-pixel warp tiles
     uint32_t n_chunks, chunk_samples;  // sample chunks per tile (1 unless the image is small)
@@ -55,7 +56,7 @@ struct RenderArgs {
     unsigned long long* stats;   // STAT_COUNT counters
 };
 
-int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh);
+int megakernel_max_blocks_per_sm(bool exhaustive, bool count, bool bvh, bool volumes);
 cudaError_t launch_megakernel(const RenderArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
 // scan.cu: BVH off + every object a sphere (scenes/benchmark.json); same RenderArgs, same results as the megakernel
 int scan_kernel_max_blocks_per_sm(bool count);
@@ -113,7 +114,7 @@ struct WfArgs {
     unsigned long long* stats;
 };
 
-int wf_extend_max_blocks_per_sm(bool exhaustive, bool count);
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes);
 cudaError_t launch_wf_begin(const WfArgs& a, cudaStream_t st);       // zero accum + wave counter
 cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st);
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);

@@ -33,11 +33,27 @@ __device__ __forceinline__ uint32_t scan_lanemask_lt() {
     return m;
 }
 
+// Philox4x32-10 (device_core.cuh) with the key schedule taken from the kernel parameters: the ten round keys are
+// launch constants, so each round is 2 IMAD.WIDE + 2 LOP3 with a constant-bank operand (the in-kernel schedule
+// cost two extra uniform adds per round, a quarter of the generator's instructions).
+__device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const RenderArgs& a) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        const uint32_t h0 = __umulhi(M0, c0), l0 = M0 * c0;
+        const uint32_t h1 = __umulhi(M1, c2), l1 = M1 * c2;
+        const uint32_t n0 = h1 ^ c1 ^ a.rk0[i], n2 = h0 ^ c3 ^ a.rk1[i];
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
 template <bool COUNT>
 __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_scan_kernel(const RenderArgs a) {
-    __shared__ uint32_t serve_tab[RTR_MEGA_THREADS / 32][32];  // per warp: lane ids of the lanes still in the rejection loop
+    // per warp: (lane | depth << 8, sample) of the lanes still in the rejection loop, in lane order
+    __shared__ uint2 serve_tab[RTR_MEGA_THREADS / 32][32];
     const uint32_t lane = threadIdx.x & 31u;
-    uint32_t* tab = serve_tab[threadIdx.x >> 5];
+    uint2* tab = serve_tab[threadIdx.x >> 5];
     const uint32_t FULL = 0xffffffffu;
     const uint32_t NONE = 0xFFFFFFFFu;
     const uint32_t lt = scan_lanemask_lt();
@@ -59,7 +75,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
         uint32_t s = a.sample_begin + chunk * a.chunk_samples;
         const uint32_t s_first = s;
         const uint32_t s_end = min(s + a.chunk_samples, a.sample_begin + a.sample_count);
-        uint32_t rays = 0, envs = 0;
+        uint32_t rays = 0, envs = 0;  // rays: warp total (every lane holds the same count)
         v3 sum = mk(0.0f, 0.0f, 0.0f);
         Ray ray; ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
         v3 T = mk(1.0f, 1.0f, 1.0f);
@@ -153,7 +169,7 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
 
             // ---------------------------------------------------------------- the one draw site  [bucket:rng]
             const uint32_t purpose = want == W_JITTER ? P_JITTER : want == W_BALL ? P_SPHERE : P_DIELECTRIC;
-            const uint4 r0 = philox4x32_10(pixel, s, (depth & 0xFFu) | (purpose << 8), 0u, a.k0, a.k1);
+            const uint4 r0 = philox_rk(pixel, s, (depth & 0xFFu) | (purpose << 8), 0u, a);
             v3 ball = mk(gen_range_m11(r0.x), gen_range_m11(r0.y), gen_range_m11(r0.z));
             bool failed = want == W_BALL && !(dot(ball, ball) <= 1.0f);
 
@@ -166,16 +182,15 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
                 const uint32_t shift = 5u - (nf <= 1u ? 0u : 32u - (uint32_t)__clz((int)(nf - 1u)));
                 const uint32_t per = 1u << shift;
                 const uint32_t my_j = (uint32_t)__popc(fail & lt);
-                if (failed) tab[my_j] = lane;
+                if (failed) tab[my_j] = make_uint2(lane | (depth << 8), s);
                 __syncwarp();
                 const uint32_t j = lane >> shift;
                 const bool serving = j < nf;
-                const uint32_t src = serving ? tab[j] : lane;
-                const uint32_t src_s = __shfl_sync(FULL, s, src);
-                const uint32_t src_depth = __shfl_sync(FULL, depth, src);
+                const uint2 served = tab[serving ? j : 0u];
+                const uint32_t src = served.x & 31u, src_depth = served.x >> 8, src_s = served.y;
                 const uint32_t src_pixel = (ty * 4u + (src >> 3)) * a.width + tx * 8u + (src & 7u);
-                const uint4 r = philox4x32_10(src_pixel, src_s, (src_depth & 0xFFu) | ((uint32_t)P_SPHERE << 8),
-                                              kbase + (lane & (per - 1u)), a.k0, a.k1);
+                const uint4 r = philox_rk(src_pixel, src_s, (src_depth & 0xFFu) | ((uint32_t)P_SPHERE << 8),
+                                          kbase + (lane & (per - 1u)), a);
                 const v3 cand = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
                 const uint32_t okm = __ballot_sync(FULL, serving && dot(cand, cand) <= 1.0f);
                 const uint32_t seg_mask = per == 32u ? FULL : ((1u << per) - 1u);
@@ -244,14 +259,14 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
 
             // ---------------------------------------------------------------- world.hit (scene.rs:141-156)  [bucket:primitive_tests]
             traced = alive;
+            rays += (uint32_t)__popc(__ballot_sync(FULL, alive));
             if (alive) {
-                ++rays;
                 float closest = RTR_INF;  // closest_so_far (scene.rs:144)
                 winner = NONE;
                 for (uint32_t i = 0; i < n_obj; ++i) {
                     const float4 sp = __ldg(spheres + i);
                     float t;
-                    if (sphere_t(sp, ray, 0.00001f, closest, t)) { closest = t; winner = i; }
+                    if (sphere_t<true>(sp, ray, 0.00001f, closest, t)) { closest = t; winner = i; }
                 }
                 hit_t = closest;
             }
@@ -267,10 +282,9 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
         n_rays += rays;
         if (COUNT) n_env += envs;
     }
+    if (COUNT) {
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        n_rays += __shfl_xor_sync(0xffffffffu, n_rays, o);
-        if (COUNT) n_env += __shfl_xor_sync(0xffffffffu, n_env, o);
+        for (int o = 16; o > 0; o >>= 1) n_env += __shfl_xor_sync(0xffffffffu, n_env, o);
     }
     if (lane == 0) {
         atomicAdd(&a.stats[STAT_RAYS], n_rays);

@@ -94,7 +94,10 @@ __global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArg
 }
 
 // ------------------------------------------------------------------ extend
-template <bool EXHAUSTIVE, bool COUNT>
+// VOLUMES = false: the scene holds no Volume and the BVH is on (every shipped scene but C5).  Volume::hit is a
+// non-inlined call with two nested walks; compiling it out of the walk removes the call's register save/restore
+// and the per-ray RNG key from the traversal state (ncu: local-memory traffic was 44 % of wf_extend's L1 wavefronts).
+template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES>
 __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_extend_kernel(const WfArgs a) {
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
     __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_THREADS];
@@ -108,7 +111,7 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_e
     uint32_t* fetch = &a.counters[WFC_FETCH + a.bounce];
     Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
 
-    if (a.enable_bvh_tree == 0u) {  // Hittable for Scene: linear scan (scene.rs:141-156), uniform work per ray
+    if (VOLUMES && a.enable_bvh_tree == 0u) {  // Hittable for Scene: linear scan (scene.rs:141-156), uniform work per ray
         for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
             const float4 o = a.in.o[i], d = a.in.d[i];
             Ray r; r.o = xyz(o); r.d = xyz(d);
@@ -137,9 +140,11 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_e
                     if (idx < n) {
                         const float4 o = a.in.o[idx], d = a.in.d[idx];
                         r.o = xyz(o); r.d = xyz(d);
-                        key.pixel = __float_as_uint(o.w);
-                        key.sample = w.begin + (__float_as_uint(d.w) >> 8);
-                        key.bounce = __float_as_uint(d.w) & 0xFFu;
+                        if (VOLUMES) {  // only Volume::hit draws inside world.hit (volume.rs:57)
+                            key.pixel = __float_as_uint(o.w);
+                            key.sample = w.begin + (__float_as_uint(d.w) >> 8);
+                            key.bounce = __float_as_uint(d.w) & 0xFFu;
+                        }
                         inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z;
                         best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
                         cur = walk_entry(a.sc.root_entry);
@@ -162,7 +167,7 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_e
                     if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
                 }
                 if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
-                    leaf_step<EXHAUSTIVE, COUNT, false>(a.sc, cur, sp, best, r, inv, 0.00001f, key, wstack, &cnt);
+                    leaf_step<EXHAUSTIVE, COUNT, false, VOLUMES>(a.sc, cur, sp, best, r, inv, 0.00001f, key, wstack, &cnt);
             } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
             // [bucket:wf_store]
             if (has && cur == RTR_REF_DONE) {
@@ -283,13 +288,24 @@ __global__ void wf_next_wave_kernel(const WfArgs a) {
 }
 
 // ------------------------------------------------------------------ launchers
-int wf_extend_max_blocks_per_sm(bool exhaustive, bool count) {
+template <typename F>
+static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, F f) {
+#define RTR_PICK(E, C, V) return f(wf_extend_kernel<E, C, V>)
+    if (exhaustive) {
+        if (count) { if (volumes) RTR_PICK(true, true, true); else RTR_PICK(true, true, false); }
+        else { if (volumes) RTR_PICK(true, false, true); else RTR_PICK(true, false, false); }
+    } else {
+        if (count) { if (volumes) RTR_PICK(false, true, true); else RTR_PICK(false, true, false); }
+        else { if (volumes) RTR_PICK(false, false, true); else RTR_PICK(false, false, false); }
+    }
+#undef RTR_PICK
+}
+
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes) {
     int n = 0;
-    cudaError_t e;
-    if (exhaustive) e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<true, true>, RTR_WF_THREADS, 0)
-                              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<true, false>, RTR_WF_THREADS, 0);
-    else e = count ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<false, true>, RTR_WF_THREADS, 0)
-                   : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, wf_extend_kernel<false, false>, RTR_WF_THREADS, 0);
+    cudaError_t e = pick_wf_extend(exhaustive, count, volumes, [&](void (*k)(const WfArgs)) {
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_WF_THREADS, 0);
+    });
     return e == cudaSuccess ? n : 0;
 }
 
@@ -305,13 +321,12 @@ cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st) {
 }
 
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st) {
-    if (exhaustive) {
-        if (count) wf_extend_kernel<true, true><<<grid, RTR_WF_THREADS, 0, st>>>(a);
-        else wf_extend_kernel<true, false><<<grid, RTR_WF_THREADS, 0, st>>>(a);
-    } else {
-        if (count) wf_extend_kernel<false, true><<<grid, RTR_WF_THREADS, 0, st>>>(a);
-        else wf_extend_kernel<false, false><<<grid, RTR_WF_THREADS, 0, st>>>(a);
-    }
+    // the generic instantiation also carries the BVH-off linear scan
+    const bool volumes = a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u;
+    pick_wf_extend(exhaustive, count, volumes, [&](void (*k)(const WfArgs)) {
+        k<<<grid, RTR_WF_THREADS, 0, st>>>(a);
+        return cudaSuccess;
+    });
     return cudaGetLastError();
 }
 
