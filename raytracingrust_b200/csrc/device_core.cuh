@@ -265,7 +265,16 @@ struct ShortStack {
 // Closest hit below `entry`; boxes are tested against (tmin, tmax), primitives as the reference does.  NESTED = a volume boundary / mesh sub-query:
 // volume leaves cannot occur there.  Volume leaves of the outer walk are handled by the caller
 // through `on_volume`.
-static __device__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+// Volume::hit is force-inlined into its callers: as a real call it cost the walk kernels ~400 bytes of spills around
+// the call site (C5: wavefront 1031 -> 1615, megakernel 697 -> 844 Mrays/s, same-box A/B), and inlined its nested walks
+// can use the 256-bit loads too (ptxas 12.9 segfaults on a NON-inlined function holding ld.global.v8 that two kernels call).
+#ifndef RTR_VOLUME_INLINE
+#define RTR_VOLUME_INLINE __forceinline__
+#endif
+#ifndef RTR_NESTED_WIDE
+#define RTR_NESTED_WIDE 1  // 256-bit loads in the nested (volume boundary) walks; set 0 together with RTR_VOLUME_INLINE=__noinline__
+#endif
+static __device__ RTR_VOLUME_INLINE float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
                             float tmin, float tmax, const RngKey& key, StackEntry* stack, bool exhaustive,
                             Counters* cnt);
 
@@ -290,8 +299,8 @@ __device__ __forceinline__ uint32_t pop_next(const STACK& stack, int& sp, float 
 // cur == RTR_REF_DONE: finished.  Callers schedule the steps: walk() (nested queries, batch kernel)
 // runs the classic "while-while" order; the render kernels pick, per warp, whichever step has more
 // lanes waiting and refill finished lanes in between (kernels.cu, wavefront.cu).
-// WIDE: fetch with 256-bit loads.  Off inside volume_hit's nested walks: ptxas 12.9 segfaults when a
-// non-inlined device function containing ld.global.v8 is called from two kernels of one module.
+// WIDE: fetch with 256-bit loads (everywhere by default; RTR_NESTED_WIDE=0 narrows the nested walks again, which a
+// non-inlined volume_hit needs: see RTR_VOLUME_INLINE above).
 template <bool EXHAUSTIVE, bool COUNT, bool WIDE = true, typename STACK>
 __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, float tmax, const STACK& stack, Counters* cnt) {
@@ -337,7 +346,7 @@ __device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cu
     if (kind == REF_TRI) {
         const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 4;
         float4 q0, q1;
-        if (!NESTED) ldg8(q, q0, q1);
+        if (!NESTED || RTR_NESTED_WIDE) ldg8(q, q0, q1);
         else { q0 = ldg4(q); q1 = ldg4(q + 1); }
         float t, u, v;
         if (COUNT) cnt->tris++;
@@ -350,7 +359,7 @@ __device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cu
         const uint32_t i = RTR_REF_INDEX(cur);
         const F4* q = sc.tris + (size_t)i * 4;
         float4 a0, a1, b0, b1;
-        if (!NESTED) { ldg8(q, a0, a1); ldg8(q + 4, b0, b1); }
+        if (!NESTED || RTR_NESTED_WIDE) { ldg8(q, a0, a1); ldg8(q + 4, b0, b1); }
         else { a0 = ldg4(q); a1 = ldg4(q + 1); b0 = ldg4(q + 4); b1 = ldg4(q + 5); }
         const float4 a2 = ldg4(q + 2), b2 = ldg4(q + 6);
         float t, u, v;
@@ -383,7 +392,7 @@ template <bool EXHAUSTIVE, bool COUNT, bool NESTED>
 __device__ __forceinline__ void walk_round(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                            const RayInv& inv, float tmin, float tmax, const RngKey& key,
                                            const LocalStack& stack, Counters* cnt) {
-    while (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT, !NESTED>(sc, cur, sp, best, r, inv, tmin, tmax, stack, cnt);
+    while (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT, !NESTED || RTR_NESTED_WIDE>(sc, cur, sp, best, r, inv, tmin, tmax, stack, cnt);
     if (cur == RTR_REF_DONE) return;
     leaf_step<EXHAUSTIVE, COUNT, NESTED>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
 }
@@ -414,7 +423,7 @@ __device__ __forceinline__ bool boundary_t(const SceneView& sc, uint32_t entry, 
 }
 
 // Volume::hit (volume.rs:35-72).  Returns t, or NaN for None.
-static __device__ __noinline__ float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+static __device__ RTR_VOLUME_INLINE float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
                                          float tmin, float tmax, const RngKey& key, StackEntry* stack,
                                          bool exhaustive, Counters* cnt) {
     const float NONE = __int_as_float(0x7fc00000);

@@ -13,7 +13,7 @@ namespace rtr {
 
 #define RTR_MEGA_THREADS 128
 #ifndef RTR_MEGA_MIN_BLOCKS
-#define RTR_MEGA_MIN_BLOCKS 7  // resident CTAs per SM the register allocation must allow (swept on B200: 4..8)
+#define RTR_MEGA_MIN_BLOCKS 8  // resident CTAs per SM the register allocation must allow (swept on B200 4..8; 8 since Volume::hit is inlined)
 #endif
 
 #ifndef RTR_MEGA_MIN_BLOCKS_SCAN
@@ -81,7 +81,10 @@ cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, u
 // surviving paths DENSELY (warp ballot + popc + one atomic per warp) into the other buffer.
 #define RTR_WF_THREADS 128
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS
-#define RTR_WF_EXTEND_MIN_BLOCKS 8
+#define RTR_WF_EXTEND_MIN_BLOCKS 8  // wf_extend with Volume::hit compiled in (64 registers)
+#endif
+#ifndef RTR_WF_EXTEND_MIN_BLOCKS_NOVOL
+#define RTR_WF_EXTEND_MIN_BLOCKS_NOVOL 9  // without it: 56 registers, swept 6..10 on B200 (9: +2..5 % over 8)
 #endif
 #define RTR_WF_MAX_DEPTH 256      // max_ray_depth is a u8 in the reference
 enum { WFC_WAVE = 0, WFC_QCOUNT = 8, WFC_FETCH = WFC_QCOUNT + RTR_WF_MAX_DEPTH + 8, WFC_WORDS = WFC_FETCH + RTR_WF_MAX_DEPTH + 8 };

@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArg
 // non-inlined call with two nested walks; compiling it out of the walk removes the call's register save/restore
 // and the per-ray RNG key from the traversal state (ncu: local-memory traffic was 44 % of wf_extend's L1 wavefronts).
 template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES>
-__global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_EXTEND_MIN_BLOCKS) wf_extend_kernel(const WfArgs a) {
+__global__ void __launch_bounds__(RTR_WF_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL) wf_extend_kernel(const WfArgs a) {
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
     __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_THREADS];
     ShortStack<RTR_SHORT_STACK, RTR_WF_THREADS> wstack;
