@@ -385,7 +385,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     const uint32_t W = p->width, H = p->height;
     const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
     const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;
-    const bool count_work = stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0;
+    const bool count_work = (stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0) || (p->flags & RTR_FLAG_REFERENCE_TREE) != 0;  // the reference-topology walk lives in the counting instantiations
     const uint64_t n_pixels = (uint64_t)W * H;
     WfArgs a;
     std::memset(&a, 0, sizeof(a));
@@ -492,7 +492,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     const uint32_t W = p->width, H = p->height;
     const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
     const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;
-    const bool count_work = stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0;
+    const bool count_work = (stats_out != nullptr && (p->flags & RTR_FLAG_COUNT_WORK) != 0) || (p->flags & RTR_FLAG_REFERENCE_TREE) != 0;  // the reference-topology walk lives in the counting instantiations
     RenderArgs a;
     std::memset(&a, 0, sizeof(a));
     a.sc = view_for(scene, p->flags);

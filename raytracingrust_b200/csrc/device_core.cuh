@@ -314,7 +314,9 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
     // traversal tree: every child slot carries a box (a leaf's slot holds its gate, flat.h); reference
     // topology: leaves carry none (bvh.rs:157-159) and are tested as soon as the parent's box was pierced
     // (a paired leaf stands for the 2-leaf Split it folds, so its box is that Split's and is tested in both modes)
-    const bool boxed_leaves = sc.reference_tree == 0u;
+    // Only the COUNT instantiations can walk the reference topology (capi.cpp selects them for RTR_FLAG_REFERENCE_TREE):
+    // the others drop the per-child uniform branch.
+    const bool boxed_leaves = COUNT ? sc.reference_tree == 0u : true;
     const uint32_t lk = RTR_REF_KIND(lref), rk = RTR_REF_KIND(rref);
     if (lh && (boxed_leaves || lk == REF_NODE || lk == REF_TRI2 || lk == REF_SPHERE2)) { lh = slab(q0, q1, r, inv, tmin, tmax, le); if (COUNT) cnt->nodes++; }
     if (rh && (boxed_leaves || rk == REF_NODE || rk == REF_TRI2 || rk == REF_SPHERE2)) { rh = slab(q2, q3, r, inv, tmin, tmax, re); if (COUNT) cnt->nodes++; }

@@ -21,6 +21,10 @@
 #include "device_core.cuh"
 #include "kernels.h"
 
+#ifndef RTR_WF_NODE_BURST
+#define RTR_WF_NODE_BURST 0  // 1: two node steps per scheduling decision
+#endif
+
 namespace rtr {
 
 __device__ __forceinline__ uint32_t lanemask_lt() {
@@ -164,7 +168,12 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BL
                     const uint32_t mn = __ballot_sync(FULL, at_node);
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
-                    if (at_node) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
+                    if (at_node) {
+                        node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
+#if RTR_WF_NODE_BURST
+                        if (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
+#endif
+                    }
                 }
                 if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
                     leaf_step<EXHAUSTIVE, COUNT, false, VOLUMES>(a.sc, cur, sp, best, r, inv, 0.00001f, key, wstack, &cnt);
