@@ -266,6 +266,13 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te[0])
 
+    # which of our kernels the megakernel selector resolved to (capi.cpp render_into): the all-sphere BVH-off scan
+    # kernel (csrc/scan.cu) when every object is a sphere and the BVH is off, as in scenes/benchmark.json
+    used = {1: "megakernel", 2: "wavefront"}[st_count["kernel_used"]]
+    kernel_fn = "render_megakernel" if used == "megakernel" else "wavefront wave sequence (wf_extend dominant)"
+    if (used == "megakernel" and not scene.settings.enable_bvh_tree and scene.settings.max_ray_depth >= 1
+            and os.environ.get("RTR_SCAN_KERNEL", "1") != "0" and all(isinstance(o, rt.Sphere) for o in scene.objects)):
+        used, kernel_fn = "megakernel (all-sphere scan kernel)", "render_scan_kernel"
     if rank == 0:
         peaks = {}
         try:
@@ -288,7 +295,7 @@ def main():
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "msamples_per_s": samples_step * args.steps / (ms * 1e-3) / 1e6,
             "rays_per_step": rays_step, "samples_per_step": samples_step,
-            "config": {"workload": desc, "kernel": {1: "megakernel", 2: "wavefront"}[st_count["kernel_used"]], "per_gpu_spp": s_count, "image_spp": total_spp, "parallelism": f"sample-slices x{world} + ncclReduce",
+            "config": {"workload": desc, "kernel": used, "per_gpu_spp": s_count, "image_spp": total_spp, "parallelism": f"sample-slices x{world} + ncclReduce",
                        "l2_policy": "each step rewrites the 33 MB accumulation buffer and traces fresh Philox paths; scene working set is L2-resident by design (SURVEY 8d)",
                        "scene_device_bytes": info["device_bytes"], "bvh_nodes": info["n_nodes"]},
             "clocks": clocks,
@@ -298,7 +305,7 @@ def main():
             # (NCCL's reduce kernel is not ours)
             "gpu_launches": args.steps * (st_count["kernel_launches"] + 1),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "kernel": "render_megakernel" if st_count["kernel_used"] == 1 else "wavefront wave sequence (wf_extend dominant)",
+                         "traffic": traffic, "peak_source": peak_src, "kernel": kernel_fn,
                          "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
                          "bytes_per_ray": alg / max(st_count["rays"], 1),
                          "traffic_note": "dram__bytes_read+write per launch of the dominant kernel from profiles/ (ncu --set full); "

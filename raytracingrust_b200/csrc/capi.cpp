@@ -38,7 +38,7 @@ struct rtr_context {
     float4* wf_state = nullptr; size_t wf_state_elems = 0;  // wavefront: 7 path streams (+ lbuf), see render_wavefront
     uint32_t* wf_counters = nullptr;
     uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
-    uint64_t wf_target_paths = 1ull << 23;  // RTR_WF_PATHS: paths in flight per wave
+    uint64_t wf_target_paths = 1ull << 24;  // RTR_WF_PATHS: paths in flight per wave (swept 2^22..2^25 on B200; 2.1 GB of path state)
     int wf_use_graph = 1;  // RTR_WF_GRAPH
     int use_scan_kernel = 1;  // RTR_SCAN_KERNEL: 0 sends all-sphere BVH-off renders through the generic megakernel
     char* batch_in = nullptr; size_t batch_in_bytes = 0;
