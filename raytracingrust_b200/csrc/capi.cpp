@@ -503,7 +503,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     a.enable_bvh_tree = p->settings.enable_bvh_tree;
     a.mode = p->settings.mode;
     a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
-    for (uint32_t i = 0; i < 10; ++i) { a.rk0[i] = a.k0 + i * 0x9E3779B9u; a.rk1[i] = a.k1 + i * 0xBB67AE85u; }
+    a.pk = make_philox_keys(a.k0, a.k1);
     a.sample_begin = p->sample_begin; a.sample_count = count;
     a.tiles_x = (W + 7) / 8;
     a.n_tiles = a.tiles_x * ((H + 3) / 4);

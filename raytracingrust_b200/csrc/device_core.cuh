@@ -555,76 +555,153 @@ __device__ __forceinline__ float reflectance(float cosine, float idx) {  // mate
 
 struct Scatter { v3 attenuation; bool some; Ray ray; };
 
-// Material::scatter for Scene.material(handle) (mode Full, render.rs:40) or the fresh
-// Lambertian(0.8) of mode Clay (render.rs:41).
-//
-// Written for SIMT convergence rather than as one function per material: lanes of a warp hold
-// different materials, so everything expensive that several materials share — the Philox draws and
-// the unit-ball rejection loop (sample.rs:44-52) — sits at ONE code site that all lanes needing any
-// draw execute together; the per-material arithmetic afterwards is a few instructions each.
-__device__ __forceinline__ Scatter scatter_event(const SceneView& sc, bool clay, uint32_t material, const Ray& ray,
-                                                 const Hit& hit, const RngKey& key) {
-    uint32_t kind = RTR_MAT_LAMBERTIAN;
-    v3 color = mk(0.8f, 0.8f, 0.8f);
-    float param = 0.0f;
+// Material::scatter for Scene.material(handle) (mode Full, render.rs:40) or the fresh Lambertian(0.8) of mode Clay
+// (render.rs:41), in three parts so that callers can put the random draws where the warp is converged:
+//   scatter_prepare   resolve MixMaterial (materials.rs:150-156), Dielectric prologue (:114-124), say which draw is needed
+//   (draw)            unit-ball rejection loop for Lambertian / Metal / Isotropic (sample.rs:44-52), one uniform for a
+//                     Dielectric that can refract (no draw under total internal reflection, Q11)
+//   scatter_finish    the per-material arithmetic, a few instructions each
+// scatter_event() strings them together with the plain sequential loop (megakernel refill, wf_shade, scatter_batch);
+// scan.cu runs the draw as ONE site for the whole warp followed by the warp-cooperative tail (coop_ball_tail).  The
+// same arrangement in wf_shade measured neutral (+1.3 % C4, -1.3 % C1: that kernel waits on memory, not on issue slots).
+struct ScatterPrep {
+    uint32_t kind;
+    v3 color;
+    float param, ratio, cos_theta;
+    v3 unit;
+    bool cannot_refract, want_ball, want_uniform;
+};
+__device__ __forceinline__ ScatterPrep scatter_prepare(const SceneView& sc, bool clay, uint32_t material, const Ray& ray,
+                                                       const Hit& hit, const RngKey& key) {
+    ScatterPrep p;
+    p.kind = RTR_MAT_LAMBERTIAN;
+    p.color = mk(0.8f, 0.8f, 0.8f);
+    p.param = 0.0f;
     if (!clay) {
         MaterialRec m = sc.materials[material];
         for (uint32_t level = 0; m.kind == RTR_MAT_MIX; ++level) {  // MixMaterial (materials.rs:150-156)
             const bool first = gen_range_01(draw(key, P_MIX, level).x) >= m.param;
             m = sc.materials[first ? m.first : m.second];
         }
-        kind = m.kind; color = mk(m.r, m.g, m.b); param = m.param;
+        p.kind = m.kind; p.color = mk(m.r, m.g, m.b); p.param = m.param;
     }
     // Dielectric prologue (materials.rs:114-124)
-    float ratio = 1.0f, cos_theta = 0.0f;
-    v3 unit = mk(0.0f, 0.0f, 0.0f);
-    bool cannot_refract = false;
-    if (kind == RTR_MAT_DIELECTRIC) {
-        ratio = hit.front_face ? 1.0f / param : param;
-        unit = normalize(ray.d);
-        cos_theta = fminf(dot(hit.normal, -unit), 1.0f);
-        const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-        cannot_refract = (ratio * sin_theta) > 1.0f;
+    p.ratio = 1.0f; p.cos_theta = 0.0f;
+    p.unit = mk(0.0f, 0.0f, 0.0f);
+    p.cannot_refract = false;
+    if (p.kind == RTR_MAT_DIELECTRIC) {
+        p.ratio = hit.front_face ? 1.0f / p.param : p.param;
+        p.unit = normalize(ray.d);
+        p.cos_theta = fminf(dot(hit.normal, -p.unit), 1.0f);
+        const float sin_theta = sqrtf(1.0f - p.cos_theta * p.cos_theta);
+        p.cannot_refract = (p.ratio * sin_theta) > 1.0f;
     }
-    // the one draw site: unit-ball rejection for Lambertian / Metal / Isotropic, a single uniform for
-    // a Dielectric that can refract (no draw under total internal reflection, Q11)
-    const bool want_ball = kind == RTR_MAT_LAMBERTIAN || kind == RTR_MAT_METAL || kind == RTR_MAT_ISOTROPIC;
-    const bool want_uniform = kind == RTR_MAT_DIELECTRIC && !cannot_refract;
-    v3 ball = mk(0.0f, 0.0f, 0.0f);
-    float xi = 0.0f;
-    if (want_ball || want_uniform) {
-        const uint32_t purpose = want_ball ? P_SPHERE : P_DIELECTRIC;
-        for (uint32_t k = 0;; ++k) {
-            const uint4 r = draw(key, purpose, k);
-            if (!want_ball) { xi = gen_range_01(r.x); break; }
-            ball = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
-            if (dot(ball, ball) <= 1.0f) break;
-        }
-    }
+    p.want_ball = p.kind == RTR_MAT_LAMBERTIAN || p.kind == RTR_MAT_METAL || p.kind == RTR_MAT_ISOTROPIC;
+    p.want_uniform = p.kind == RTR_MAT_DIELECTRIC && !p.cannot_refract;
+    return p;
+}
+__device__ __forceinline__ Scatter scatter_finish(const ScatterPrep& p, v3 ball, float xi, const Ray& ray, const Hit& hit) {
     Scatter s;
     s.ray.o = hit.point;
     s.ray.d = mk(0.0f, 0.0f, 0.0f);
-    s.attenuation = color;
+    s.attenuation = p.color;
     s.some = true;
-    if (kind == RTR_MAT_LAMBERTIAN) {  // materials.rs:31-41
+    if (p.kind == RTR_MAT_LAMBERTIAN) {  // materials.rs:31-41
         v3 dir = hit.normal + normalize(ball);
         if (near_zero(dir)) dir = hit.normal;
         s.ray.d = dir;
-    } else if (kind == RTR_MAT_METAL) {  // :58-70
+    } else if (p.kind == RTR_MAT_METAL) {  // :58-70
         const v3 reflected = normalize(reflect(ray.d, hit.normal));
-        s.ray.d = reflected + param * normalize(ball);
+        s.ray.d = reflected + p.param * normalize(ball);
         s.some = dot(s.ray.d, hit.normal) > 0.0f;
         if (!s.some) s.attenuation = mk(0.0f, 0.0f, 0.0f);
-    } else if (kind == RTR_MAT_DIELECTRIC) {  // :125-138
-        const bool refl = cannot_refract || reflectance(cos_theta, ratio) > xi;
-        s.ray.d = refl ? reflect(unit, hit.normal) : refract(unit, hit.normal, ratio);
+    } else if (p.kind == RTR_MAT_DIELECTRIC) {  // :125-138
+        const bool refl = p.cannot_refract || reflectance(p.cos_theta, p.ratio) > xi;
+        s.ray.d = refl ? reflect(p.unit, hit.normal) : refract(p.unit, hit.normal, p.ratio);
         s.attenuation = mk(1.0f, 1.0f, 1.0f);
-    } else if (kind == RTR_MAT_ISOTROPIC) {  // volume.rs:82-87
+    } else if (p.kind == RTR_MAT_ISOTROPIC) {  // volume.rs:82-87
         s.ray.d = ball;
     } else {  // Emission (:88-90)
         s.some = false;
     }
     return s;
+}
+__device__ __forceinline__ Scatter scatter_event(const SceneView& sc, bool clay, uint32_t material, const Ray& ray,
+                                                 const Hit& hit, const RngKey& key) {
+    const ScatterPrep p = scatter_prepare(sc, clay, material, ray, hit, key);
+    // the one draw site: lanes holding different materials still converge on the expensive part
+    v3 ball = mk(0.0f, 0.0f, 0.0f);
+    float xi = 0.0f;
+    if (p.want_ball || p.want_uniform) {
+        const uint32_t purpose = p.want_ball ? P_SPHERE : P_DIELECTRIC;
+        for (uint32_t k = 0;; ++k) {
+            const uint4 r = draw(key, purpose, k);
+            if (!p.want_ball) { xi = gen_range_01(r.x); break; }
+            ball = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
+            if (dot(ball, ball) <= 1.0f) break;
+        }
+    }
+    return scatter_finish(p, ball, xi, ray, hit);
+}
+
+// ------------------------------------------------------------------ warp-cooperative rejection tail  [bucket:rng]
+// Philox4x32-10 with the key schedule taken from the kernel parameters: the ten round keys (k + i*W) are launch
+// constants, so each round is 2 IMAD.WIDE + 2 LOP3 with a constant-bank operand (the in-kernel schedule costs two
+// extra uniform adds per round, a quarter of the generator's instructions).
+__device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const PhiloxKeys& pk) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        const uint32_t h0 = __umulhi(M0, c0), l0 = M0 * c0;
+        const uint32_t h1 = __umulhi(M1, c2), l1 = M1 * c2;
+        const uint32_t n0 = h1 ^ c1 ^ pk.rk0[i], n2 = h0 ^ c3 ^ pk.rk1[i];
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ uint32_t warp_lanemask_lt() {
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+// Continues the unit-ball rejection loop (sample.rs:44-52) of the lanes whose candidate 0 was rejected (`failed`;
+// 47.6 % of them).  Counter-based RNG: any lane can compute candidate k of any lane's stream, so all 32 lanes serve
+// the failing ones, `per` candidates each (the largest power of two with failing * per <= 32), and a failing lane
+// takes the FIRST accepted k of its segment — exactly the sequential loop's result, in two or three full-width
+// rounds instead of five or six thin ones.  Must be called by the whole warp; `tab` = 32 uint4 of shared memory per
+// warp; (pixel, sample, depth) name the lane's stream (draw(key, P_SPHERE, k)).
+__device__ __forceinline__ void coop_ball_tail(bool failed, uint32_t pixel, uint32_t sample, uint32_t depth, uint4* tab,
+                                               const PhiloxKeys& pk, v3& ball) {
+    const uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt = warp_lanemask_lt();
+    uint32_t fail = __ballot_sync(FULL, failed);
+    uint32_t kbase = 1u;
+    while (fail != 0u) {
+        const uint32_t nf = (uint32_t)__popc(fail);
+        const uint32_t shift = 5u - (nf <= 1u ? 0u : 32u - (uint32_t)__clz((int)(nf - 1u)));
+        const uint32_t per = 1u << shift;
+        const uint32_t my_j = (uint32_t)__popc(fail & lt);
+        if (failed) tab[my_j] = make_uint4(pixel, sample, depth, 0u);
+        __syncwarp();
+        const uint32_t j = lane >> shift;
+        const bool serving = j < nf;
+        const uint4 served = tab[serving ? j : 0u];
+        const uint4 r = philox_rk(served.x, served.y, (served.z & 0xFFu) | ((uint32_t)P_SPHERE << 8),
+                                  kbase + (lane & (per - 1u)), pk);
+        const v3 cand = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
+        const uint32_t okm = __ballot_sync(FULL, serving && dot(cand, cand) <= 1.0f);
+        const uint32_t seg_mask = per == 32u ? FULL : ((1u << per) - 1u);
+        const uint32_t seg = failed ? (okm >> (my_j << shift)) & seg_mask : 0u;
+        const uint32_t from = seg != 0u ? (my_j << shift) + (uint32_t)(__ffs((int)seg) - 1) : lane;
+        const float bx = __shfl_sync(FULL, cand.x, from);
+        const float by = __shfl_sync(FULL, cand.y, from);
+        const float bz = __shfl_sync(FULL, cand.z, from);
+        if (seg != 0u) { ball = mk(bx, by, bz); failed = false; }
+        fail = __ballot_sync(FULL, failed);
+        kbase += per;
+        __syncwarp();
+    }
 }
 
 // ------------------------------------------------------------------ backgrounds (backgrounds.rs)  [bucket:background]

@@ -33,6 +33,14 @@ struct v3 { float x, y, z; };
 // RayOrigin (lib/core/camera.rs:11-16), computed once per render on the host
 struct CameraBasis { v3 origin, horizontal, vertical, lower_left_corner; };
 
+// the ten Philox4x32-10 round keys (seed + i * Weyl constant), filled by the host once per launch
+struct PhiloxKeys { uint32_t rk0[10], rk1[10]; };
+inline PhiloxKeys make_philox_keys(uint32_t k0, uint32_t k1) {
+    PhiloxKeys pk;
+    for (uint32_t i = 0; i < 10; ++i) { pk.rk0[i] = k0 + i * 0x9E3779B9u; pk.rk1[i] = k1 + i * 0xBB67AE85u; }
+    return pk;
+}
+
 enum { STAT_RAYS = 0, STAT_NODES = 1, STAT_TRIS = 2, STAT_SPHERES = 3, STAT_ENV = 4, STAT_COUNT = 8 };
 
 struct RenderArgs {
@@ -44,7 +52,7 @@ struct RenderArgs {
     uint32_t enable_bvh_tree;
     uint32_t mode;
     uint32_t k0, k1;             // Philox key = seed
-    uint32_t rk0[10], rk1[10];   // the ten Philox round keys (k + i*W): LOP3 reads them straight from the constant bank
+    PhiloxKeys pk;               // round keys of (k0, k1): LOP3 reads them straight from the constant bank
     uint32_t sample_begin, sample_count;
     uint32_t tiles_x, n_tiles;   // 8x4-pixel warp tiles
     uint32_t n_chunks, chunk_samples;  // sample chunks per tile (1 unless the image is small)

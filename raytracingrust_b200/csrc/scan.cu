@@ -27,36 +27,13 @@ namespace rtr {
 
 enum { W_NONE = 0, W_JITTER = 1, W_BALL = 2, W_UNIFORM = 3 };
 
-__device__ __forceinline__ uint32_t scan_lanemask_lt() {
-    uint32_t m;
-    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
-    return m;
-}
-
-// Philox4x32-10 (device_core.cuh) with the key schedule taken from the kernel parameters: the ten round keys are
-// launch constants, so each round is 2 IMAD.WIDE + 2 LOP3 with a constant-bank operand (the in-kernel schedule
-// cost two extra uniform adds per round, a quarter of the generator's instructions).
-__device__ __forceinline__ uint4 philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const RenderArgs& a) {
-    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u;
-#pragma unroll
-    for (int i = 0; i < 10; ++i) {
-        const uint32_t h0 = __umulhi(M0, c0), l0 = M0 * c0;
-        const uint32_t h1 = __umulhi(M1, c2), l1 = M1 * c2;
-        const uint32_t n0 = h1 ^ c1 ^ a.rk0[i], n2 = h0 ^ c3 ^ a.rk1[i];
-        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
-    }
-    return make_uint4(c0, c1, c2, c3);
-}
-
 template <bool COUNT>
 __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_scan_kernel(const RenderArgs a) {
-    // per warp: (lane | depth << 8, sample) of the lanes still in the rejection loop, in lane order
-    __shared__ uint2 serve_tab[RTR_MEGA_THREADS / 32][32];
+    __shared__ uint4 serve_tab[RTR_MEGA_THREADS / 32][32];  // coop_ball_tail's per-warp table
     const uint32_t lane = threadIdx.x & 31u;
-    uint2* tab = serve_tab[threadIdx.x >> 5];
+    uint4* tab = serve_tab[threadIdx.x >> 5];
     const uint32_t FULL = 0xffffffffu;
     const uint32_t NONE = 0xFFFFFFFFu;
-    const uint32_t lt = scan_lanemask_lt();
     unsigned long long n_rays = 0, n_env = 0;
     const SceneView& sc = a.sc;
     const uint32_t n_obj = sc.n_objects;
@@ -169,41 +146,11 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
 
             // ---------------------------------------------------------------- the one draw site  [bucket:rng]
             const uint32_t purpose = want == W_JITTER ? P_JITTER : want == W_BALL ? P_SPHERE : P_DIELECTRIC;
-            const uint4 r0 = philox_rk(pixel, s, (depth & 0xFFu) | (purpose << 8), 0u, a);
+            const uint4 r0 = philox_rk(pixel, s, (depth & 0xFFu) | (purpose << 8), 0u, a.pk);
             v3 ball = mk(gen_range_m11(r0.x), gen_range_m11(r0.y), gen_range_m11(r0.z));
-            bool failed = want == W_BALL && !(dot(ball, ball) <= 1.0f);
 
-            // ---------------------------------------------------------------- cooperative rejection tail
-            uint32_t fail = __ballot_sync(FULL, failed);
-            uint32_t kbase = 1u;
-            while (fail != 0u) {
-                const uint32_t nf = (uint32_t)__popc(fail);
-                // candidates per failing lane this round: the largest power of two with nf * per <= 32
-                const uint32_t shift = 5u - (nf <= 1u ? 0u : 32u - (uint32_t)__clz((int)(nf - 1u)));
-                const uint32_t per = 1u << shift;
-                const uint32_t my_j = (uint32_t)__popc(fail & lt);
-                if (failed) tab[my_j] = make_uint2(lane | (depth << 8), s);
-                __syncwarp();
-                const uint32_t j = lane >> shift;
-                const bool serving = j < nf;
-                const uint2 served = tab[serving ? j : 0u];
-                const uint32_t src = served.x & 31u, src_depth = served.x >> 8, src_s = served.y;
-                const uint32_t src_pixel = (ty * 4u + (src >> 3)) * a.width + tx * 8u + (src & 7u);
-                const uint4 r = philox_rk(src_pixel, src_s, (src_depth & 0xFFu) | ((uint32_t)P_SPHERE << 8),
-                                          kbase + (lane & (per - 1u)), a);
-                const v3 cand = mk(gen_range_m11(r.x), gen_range_m11(r.y), gen_range_m11(r.z));
-                const uint32_t okm = __ballot_sync(FULL, serving && dot(cand, cand) <= 1.0f);
-                const uint32_t seg_mask = per == 32u ? FULL : ((1u << per) - 1u);
-                const uint32_t seg = failed ? (okm >> (my_j << shift)) & seg_mask : 0u;
-                const uint32_t from = seg != 0u ? (my_j << shift) + (uint32_t)(__ffs((int)seg) - 1) : lane;
-                const float bx = __shfl_sync(FULL, cand.x, from);
-                const float by = __shfl_sync(FULL, cand.y, from);
-                const float bz = __shfl_sync(FULL, cand.z, from);
-                if (seg != 0u) { ball = mk(bx, by, bz); failed = false; }
-                fail = __ballot_sync(FULL, failed);
-                kbase += per;
-                __syncwarp();
-            }
+            // ---------------------------------------------------------------- cooperative rejection tail (device_core.cuh)
+            coop_ball_tail(want == W_BALL && !(dot(ball, ball) <= 1.0f), pixel, s, depth, tab, a.pk, ball);
 
             // ---------------------------------------------------------------- epilogue
             bool late = false;  // the path ended after its draw (absorbed Metal, or Metal at the depth limit)
