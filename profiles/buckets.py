@@ -11,7 +11,7 @@ def line_buckets():
     import os
     root = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "raytracingrust_b200", "csrc")
     out = {}
-    for fn in ("device_core.cuh", "kernels.cu", "scan.cu", "wavefront.cu"):
+    for fn in ("device_core.cuh", "kernels.cu", "scan.cu", "wavefront.cu"):  # marker comments [bucket:NAME]
         path = os.path.join(root, fn)
         if not os.path.exists(path):
             continue

@@ -282,9 +282,9 @@ static __device__ RTR_VOLUME_INLINE float volume_hit(const SceneView& sc, const 
 
 // pop the next stack entry that survives t-culling
 template <bool EXHAUSTIVE, typename STACK>
-__device__ __forceinline__ uint32_t pop_next(const STACK& stack, int& sp, float best_t) {
+__device__ __forceinline__ uint32_t pop_next(const STACK& stack, int& sp, float best_t, int floor = 0) {
     const float lim = cull_limit(best_t);
-    while (sp > 0) {
+    while (sp > floor) {  // floor > 0: a nested walk stacked on top of a suspended outer walk (wf_extend, volumes)
         --sp;
         const StackEntry e = stack.get(sp);
         if (EXHAUSTIVE || !(e.enter > lim)) return e.ref;
@@ -303,7 +303,8 @@ __device__ __forceinline__ uint32_t pop_next(const STACK& stack, int& sp, float 
 // non-inlined volume_hit needs: see RTR_VOLUME_INLINE above).
 template <bool EXHAUSTIVE, bool COUNT, bool WIDE = true, typename STACK>
 __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
-                                          const RayInv& inv, float tmin, float tmax, const STACK& stack, Counters* cnt) {
+                                          const RayInv& inv, float tmin, float tmax, const STACK& stack, Counters* cnt,
+                                          int floor = 0) {
     const F4* q = sc.nodes + (size_t)RTR_REF_INDEX(cur) * 4;
     float4 q0, q1, q2, q3;
     if (WIDE) { ldg8(q, q0, q1); ldg8(q + 2, q2, q3); }
@@ -334,7 +335,7 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
     } else if (rh) {
         cur = rref;
     } else {
-        cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
+        cur = pop_next<EXHAUSTIVE>(stack, sp, best.t, floor);
     }
 }
 
@@ -384,9 +385,9 @@ __device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cu
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED, bool VOLUMES = true, typename STACK>
 __device__ __forceinline__ void leaf_step(const SceneView& sc, uint32_t& cur, int& sp, LiteHit& best, const Ray& r,
                                           const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
-                                          Counters* cnt) {
+                                          Counters* cnt, int floor = 0) {
     leaf_test<EXHAUSTIVE, COUNT, NESTED, VOLUMES>(sc, cur, sp, best, r, inv, tmin, key, stack, cnt);
-    cur = pop_next<EXHAUSTIVE>(stack, sp, best.t);
+    cur = pop_next<EXHAUSTIVE>(stack, sp, best.t, floor);
 }
 
 // one "while-while" round: all lanes descend interior nodes together, then test their pending leaf together  [bucket:nested_walk]
@@ -424,15 +425,10 @@ __device__ __forceinline__ bool boundary_t(const SceneView& sc, uint32_t entry, 
     return best.ref != REF_EMPTY_VALUE;
 }
 
-// Volume::hit (volume.rs:35-72).  Returns t, or NaN for None.
-static __device__ RTR_VOLUME_INLINE float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
-                                         float tmin, float tmax, const RngKey& key, StackEntry* stack,
-                                         bool exhaustive, Counters* cnt) {
+// The rest of Volume::hit once both boundary crossings t1, t2 are known (volume.rs:39-72).  Returns t, or NaN for None.
+__device__ __forceinline__ float volume_sample(const VolumeRec& vol, const Ray& r, float t1, float t2, float tmin, float tmax,
+                                               const RngKey& key) {
     const float NONE = __int_as_float(0x7fc00000);
-    float t1, t2;
-    const uint32_t entry = sc.reference_tree ? vol.entry_reference : vol.entry;
-    if (!boundary_t(sc, entry, r, inv, -RTR_INF, stack, exhaustive, cnt, t1)) return NONE;
-    if (!boundary_t(sc, entry, r, inv, t1 + tmin, stack, exhaustive, cnt, t2)) return NONE;
     if (t1 < tmin) t1 = tmin;
     if (t2 > tmax) t2 = tmax;
     if (t1 >= t2) return NONE;
@@ -443,6 +439,18 @@ static __device__ RTR_VOLUME_INLINE float volume_hit(const SceneView& sc, const 
     float hit_distance = vol.neg_inv_density * logf(random_float);
     if (hit_distance > distance_inside_boundary) return NONE;
     return t1 + hit_distance / ray_length;
+}
+
+// Volume::hit (volume.rs:35-72).  Returns t, or NaN for None.
+static __device__ RTR_VOLUME_INLINE float volume_hit(const SceneView& sc, const VolumeRec& vol, const Ray& r, const RayInv& inv,
+                                         float tmin, float tmax, const RngKey& key, StackEntry* stack,
+                                         bool exhaustive, Counters* cnt) {
+    const float NONE = __int_as_float(0x7fc00000);
+    float t1, t2;
+    const uint32_t entry = sc.reference_tree ? vol.entry_reference : vol.entry;
+    if (!boundary_t(sc, entry, r, inv, -RTR_INF, stack, exhaustive, cnt, t1)) return NONE;
+    if (!boundary_t(sc, entry, r, inv, t1 + tmin, stack, exhaustive, cnt, t2)) return NONE;
+    return volume_sample(vol, r, t1, t2, tmin, tmax, key);
 }
 
 // world.hit(ray, tmin, +INF) with the BVH (bvh.rs:47-49) or the linear scan (scene.rs:141-156)

@@ -132,6 +132,15 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BL
         RayInv inv; inv.ix = inv.iy = inv.iz = 0.0f;
         RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = key.sample = key.bounce = 0;
         LiteHit best; best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+        // Volume::hit as part of the lane's resumable walk (VOLUMES only).  A lane that reaches a Volume leaf does not
+        // run the two boundary queries of volume.rs:36-37 as nested loops while the rest of the warp waits (ncu on C5:
+        // 3.4 of 32 lanes per instruction); it SUSPENDS its outer walk — the outer best hit goes onto its traversal
+        // stack, `floor` marks the stack level the nested walk must not pop below — and walks the boundary with the
+        // same node / leaf steps the other lanes are taking: phase 1 over (-inf, +inf), phase 2 from t1 + tmin.  When
+        // phase 2 ends the medium is sampled (volume_sample), the outer walk is restored and offered the hit.
+        uint32_t vstate = 0u;       // 0: outer walk; else phase (1 | 2) << 30 | index in volumes[]
+        int floor = 0;              // the nested walk's stack bottom
+        float tmin_cur = 0.00001f;  // tmin of the walk in progress (render.rs:38; volume.rs:36-37)
         for (;;) {
             // ---- refill idle lanes from the stream: one atomic per warp  [bucket:wf_fetch]
             const uint32_t idle = __ballot_sync(FULL, !has);
@@ -153,6 +162,7 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BL
                         best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
                         cur = walk_entry(a.sc.root_entry);
                         sp = 0;
+                        if (VOLUMES) { vstate = 0u; floor = 0; tmin_cur = 0.00001f; }
                         has = true;
                     }
                 }
@@ -169,14 +179,61 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BL
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
                     if (at_node) {
-                        node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
+                        node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : 0.00001f, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
 #if RTR_WF_NODE_BURST
-                        if (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, 0.00001f, RTR_INF, wstack, &cnt);
+                        if (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : 0.00001f, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
 #endif
                     }
                 }
-                if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE)
-                    leaf_step<EXHAUSTIVE, COUNT, false, VOLUMES>(a.sc, cur, sp, best, r, inv, 0.00001f, key, wstack, &cnt);
+                if (RTR_REF_KIND(cur) != REF_NODE && cur != RTR_REF_DONE) {
+                    if (VOLUMES && RTR_REF_KIND(cur) == REF_VOLUME && vstate == 0u) {  // [bucket:volume_fsm]
+                        const uint32_t vidx = RTR_REF_INDEX(cur);
+                        const VolumeRec& vol = a.sc.volumes[vidx];
+                        const uint32_t entry = walk_entry(a.sc.reference_tree ? vol.entry_reference : vol.entry);
+                        if (entry == RTR_REF_DONE) {  // empty boundary: Volume::hit is None
+                            cur = pop_next<EXHAUSTIVE>(wstack, sp, best.t, 0);
+                        } else {  // suspend the outer walk, start boundary.hit(ray, -inf, +inf)  (volume.rs:36)
+                            wstack.put(sp, best.ref, best.t); ++sp;
+                            wstack.put(sp, __float_as_uint(best.u), best.v); ++sp;
+                            floor = sp;
+                            vstate = (1u << 30) | vidx;
+                            tmin_cur = -RTR_INF;
+                            best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+                            cur = entry;
+                        }
+                    } else {
+                        // nested walks never meet a Volume leaf (flat.h: a boundary is a sphere or a mesh)
+                        leaf_step<EXHAUSTIVE, COUNT, false, false>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : 0.00001f, key, wstack, &cnt, VOLUMES ? floor : 0);
+                    }
+                }
+                if (VOLUMES && vstate != 0u && cur == RTR_REF_DONE) {  // a boundary query has finished  [bucket:volume_fsm]
+                    const uint32_t vidx = vstate & 0x3FFFFFFFu;
+                    const VolumeRec& vol = a.sc.volumes[vidx];
+                    const bool second = (vstate >> 30) == 2u;
+                    if (!second && best.ref != REF_EMPTY_VALUE) {  // boundary.hit(ray, t1 + tmin, +inf)  (volume.rs:37)
+                        const float t1 = best.t;
+                        wstack.put(sp, 0u, t1); ++sp;
+                        floor = sp;
+                        vstate = (2u << 30) | vidx;
+                        tmin_cur = t1 + 0.00001f;
+                        best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
+                        cur = walk_entry(a.sc.reference_tree ? vol.entry_reference : vol.entry);
+                    } else {
+                        float t_hit = __int_as_float(0x7fc00000);  // None
+                        int base = floor;                          // stack level of the saved outer hit + 2
+                        if (second) {
+                            base = floor - 1;
+                            if (best.ref != REF_EMPTY_VALUE)
+                                t_hit = volume_sample(vol, r, wstack.get(floor - 1).enter, best.t, 0.00001f, RTR_INF, key);
+                        }
+                        const StackEntry uv = wstack.get(base - 1), tr = wstack.get(base - 2);
+                        sp = base - 2;
+                        best.t = tr.enter; best.ref = tr.ref; best.u = __uint_as_float(uv.ref); best.v = uv.enter;
+                        if (t_hit == t_hit) offer(a.sc, best, t_hit, RTR_MAKE_REF(REF_VOLUME, vidx), 0.0f, 0.0f);
+                        vstate = 0u; floor = 0; tmin_cur = 0.00001f;
+                        cur = pop_next<EXHAUSTIVE>(wstack, sp, best.t, 0);
+                    }
+                }
             } while ((uint32_t)__popc(__ballot_sync(FULL, cur != RTR_REF_DONE)) >= keep);
             // [bucket:wf_store]
             if (has && cur == RTR_REF_DONE) {
