@@ -203,20 +203,20 @@ bool device_build_applies(const rtr_scene_desc& d) {
     return true;
 }
 
-cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, DeviceBvh* out, std::vector<void*>& allocs) {
+cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs) {
     const uint32_t n = d.n_objects;
     cudaError_t e = cudaSuccess;
     std::vector<void*> scratch;
     auto alloc = [&](size_t bytes, bool keep) -> void* {
         void* p = nullptr;
         if (e != cudaSuccess) return nullptr;
-        e = cudaMalloc(&p, bytes ? bytes : 16);
+        e = cudaMallocFromPoolAsync(&p, bytes ? bytes : 16, pool, st);  // stream-ordered, reused across uploads
         if (e != cudaSuccess) return nullptr;
         (keep ? allocs : scratch).push_back(p);
         if (keep) out->device_bytes += bytes;
         return p;
     };
-    auto cleanup = [&]() { for (void* p : scratch) cudaFree(p); };
+    auto cleanup = [&]() { for (void* p : scratch) cudaFreeAsync(p, st); };
 
     // inputs by object handle (Scene.objects order; an object is a reference into spheres[])
     std::vector<float4> h_sph(n);

@@ -28,7 +28,7 @@ bool device_build_applies(const rtr_scene_desc& d);
 
 // Builds the reference tree (bvh.rs:59-144) for Scene.objects on `st`.  The four result arrays are cudaMalloc'ed
 // and appended to `allocs` (owned by the caller); scratch is freed before returning.  Synchronises `st`.
-cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, DeviceBvh* out, std::vector<void*>& allocs);
+cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs);
 
 }  // namespace rtr
 #endif

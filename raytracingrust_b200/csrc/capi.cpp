@@ -28,6 +28,9 @@ struct rtr_context {
     bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
+    // scene arrays and build scratch come from this stream-ordered pool (release threshold: never): a scene upload is
+    // ~30 allocations, and plain cudaMalloc / cudaFree stalled for 0.3-0.6 s at random while multi-GB buffers were live
+    cudaMemPool_t pool = nullptr;
     uint32_t refill_threshold = 12;  // tuning knob (RTR_REFILL_THRESHOLD), see DESIGN.md
     uint32_t* work_counter = nullptr;
     unsigned long long* stats = nullptr;  // STAT_COUNT
@@ -144,6 +147,17 @@ rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
     CU(cudaEventCreate(&ctx->ev0));
     CU(cudaEventCreate(&ctx->ev1));
     CU(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+    {
+        cudaMemPoolProps props;
+        std::memset(&props, 0, sizeof(props));
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        CU(cudaMemPoolCreate(&ctx->pool, &props));
+        unsigned long long keep = ~0ull;
+        CU(cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     if (const char* e = std::getenv("RTR_REFILL_THRESHOLD")) {
         int v = std::atoi(e);
         ctx->refill_threshold = (uint32_t)(v < 1 ? 1 : v > 32 ? 32 : v);
@@ -172,6 +186,7 @@ void rtr_context_destroy(rtr_context* ctx) {
     cudaFree(ctx->wf_state); cudaFree(ctx->wf_counters);
     cudaFree(ctx->work_counter); cudaFree(ctx->stats); cudaFree(ctx->accum); cudaFree(ctx->partials);
     cudaFree(ctx->rgba); cudaFree(ctx->batch_in); cudaFree(ctx->batch_in2); cudaFree(ctx->batch_out);
+    if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -194,7 +209,7 @@ static cudaError_t upload(rtr_scene* s, const std::vector<T>& v, const T** dst, 
     size_t bytes = v.size() * sizeof(T);
     if (bytes == 0) bytes = sizeof(T);  // keep pointers valid
     void* p = nullptr;
-    cudaError_t e = cudaMalloc(&p, bytes);
+    cudaError_t e = cudaMallocFromPoolAsync(&p, bytes, s->ctx->pool, st);
     if (e != cudaSuccess) return e;
     s->allocs.push_back(p);
     s->device_bytes += bytes;
@@ -260,17 +275,17 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
         const size_t n_tex = desc->background.kind == RTR_BG_SKYMAP ? (size_t)desc->background.width * desc->background.height : 0;
         void* env = nullptr;
         float* raw = nullptr;
-        step(cudaMalloc(&env, (n_tex ? n_tex : 1) * sizeof(float4)));
+        step(cudaMallocFromPoolAsync(&env, (n_tex ? n_tex : 1) * sizeof(float4), ctx->pool, ctx->stream));
         if (env) { s->allocs.push_back(env); s->device_bytes += (n_tex ? n_tex : 1) * sizeof(float4); }
         v.env = (const F4*)env;
         if (n_tex && e == cudaSuccess) {
-            step(cudaMalloc((void**)&raw, n_tex * 3 * sizeof(float)));
+            step(cudaMallocFromPoolAsync((void**)&raw, n_tex * 3 * sizeof(float), ctx->pool, ctx->stream));
             if (raw) {
                 step(cudaMemcpyAsync(raw, desc->background.texels, n_tex * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
                 step(launch_expand_env(raw, (float4*)env, n_tex, ctx->stream));
                 s->h2d_bytes += n_tex * 3 * sizeof(float);
-                step(cudaStreamSynchronize(ctx->stream));
-                cudaFree(raw);
+                step(cudaStreamSynchronize(ctx->stream));  // the caller's texels may die at return
+                cudaFreeAsync(raw, ctx->stream);
             }
         }
     }
@@ -304,7 +319,7 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
     }
     if (on_device) {
         DeviceBvh bvh;
-        cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, &bvh, s->allocs);
+        cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, ctx->pool, &bvh, s->allocs);
         if (be != cudaSuccess) { rtr_scene_destroy(s); return cuda_fail(ctx, be, "device BVH build"); }
         if (bvh.nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
         if (bvh.max_depth + 2 > 48) { rtr_scene_destroy(s); return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack"); }
@@ -324,7 +339,10 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
 void rtr_scene_destroy(rtr_scene* s) {
     if (!s) return;
     if (s->ctx) { cudaSetDevice(s->ctx->device); cudaStreamSynchronize(s->ctx->stream); }
-    for (void* p : s->allocs) cudaFree(p);
+    for (void* p : s->allocs) {
+        if (s->ctx) cudaFreeAsync(p, s->ctx->stream);  // back into the context's pool
+        else cudaFree(p);
+    }
     delete s;
 }
 

@@ -11,7 +11,7 @@ scene = bench.make_scene(name); scene.settings.samples_per_pixel = spp
 W, H = bench.WORKLOADS[name][1:3]
 ctx = rt.Context(0)
 host = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
-for it in range(3):
+for it in range(int(sys.argv[3]) if len(sys.argv) > 3 else 3):
     t0 = time.perf_counter(); low = scene.lower(); t1 = time.perf_counter()
     ds = ctx.upload(low); t2 = time.perf_counter()
     info = ds.info()
