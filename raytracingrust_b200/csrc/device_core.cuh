@@ -346,36 +346,43 @@ __device__ __forceinline__ void leaf_test(const SceneView& sc, const uint32_t cu
                                           const RayInv& inv, float tmin, const RngKey& key, const STACK& stack,
                                           Counters* cnt) {
     const uint32_t kind = RTR_REF_KIND(cur);
-    if (kind == REF_TRI) {
-        const F4* q = sc.tris + (size_t)RTR_REF_INDEX(cur) * 4;
-        float4 q0, q1;
-        if (!NESTED || RTR_NESTED_WIDE) ldg8(q, q0, q1);
-        else { q0 = ldg4(q); q1 = ldg4(q + 1); }
-        float t, u, v;
-        if (COUNT) cnt->tris++;
-        if (triangle_t(q0, q1, ldg4(q + 2), r, tmin, t, u, v)) offer(sc, best, t, cur, u, v);
-    } else if (kind == REF_SPHERE) {
-        float t;
-        if (COUNT) cnt->spheres++;
-        if (sphere_t(ldg4(sc.spheres + RTR_REF_INDEX(cur)), r, tmin, RTR_INF, t)) offer(sc, best, t, cur, 0.0f, 0.0f);
-    } else if (kind == REF_TRI2) {  // two sibling triangles behind one gate (traversal tree)
+    // A single leaf and a paired leaf share their first test: lanes holding either kind run it together, the second
+    // primitive of a pair follows (handled as separate branches the two kinds serialised: three tests' worth of
+    // instructions per leaf step instead of two).
+    if (kind == REF_TRI || kind == REF_TRI2) {
         const uint32_t i = RTR_REF_INDEX(cur);
         const F4* q = sc.tris + (size_t)i * 4;
-        float4 a0, a1, b0, b1;
-        if (!NESTED || RTR_NESTED_WIDE) { ldg8(q, a0, a1); ldg8(q + 4, b0, b1); }
-        else { a0 = ldg4(q); a1 = ldg4(q + 1); b0 = ldg4(q + 4); b1 = ldg4(q + 5); }
-        const float4 a2 = ldg4(q + 2), b2 = ldg4(q + 6);
+        float4 a0, a1;
+        if (!NESTED || RTR_NESTED_WIDE) ldg8(q, a0, a1);
+        else { a0 = ldg4(q); a1 = ldg4(q + 1); }
+        const float4 a2 = ldg4(q + 2);
+        const bool pair = kind == REF_TRI2;  // the sibling behind the same gate (traversal tree)
+        float4 b0 = a0, b1 = a1, b2 = a2;
+        if (pair) {  // fetched before the first test runs, so the two records' latencies overlap
+            if (!NESTED || RTR_NESTED_WIDE) ldg8(q + 4, b0, b1);
+            else { b0 = ldg4(q + 4); b1 = ldg4(q + 5); }
+            b2 = ldg4(q + 6);
+        }
         float t, u, v;
-        if (COUNT) cnt->tris += 2;
+        if (COUNT) cnt->tris++;
         if (triangle_t(a0, a1, a2, r, tmin, t, u, v)) offer(sc, best, t, RTR_MAKE_REF(REF_TRI, i), u, v);
-        if (triangle_t(b0, b1, b2, r, tmin, t, u, v)) offer(sc, best, t, RTR_MAKE_REF(REF_TRI, i + 1), u, v);
-    } else if (kind == REF_SPHERE2) {
+        if (pair) {
+            if (COUNT) cnt->tris++;
+            if (triangle_t(b0, b1, b2, r, tmin, t, u, v)) offer(sc, best, t, RTR_MAKE_REF(REF_TRI, i + 1), u, v);
+        }
+    } else if (kind == REF_SPHERE || kind == REF_SPHERE2) {
         const uint32_t i = RTR_REF_INDEX(cur);
-        const float4 s0 = ldg4(sc.spheres + i), s1 = ldg4(sc.spheres + i + 1);
+        const bool pair = kind == REF_SPHERE2;
+        const float4 s0 = ldg4(sc.spheres + i);
+        float4 s1 = s0;
+        if (pair) s1 = ldg4(sc.spheres + i + 1);
         float t;
-        if (COUNT) cnt->spheres += 2;
+        if (COUNT) cnt->spheres++;
         if (sphere_t(s0, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i), 0.0f, 0.0f);
-        if (sphere_t(s1, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i + 1), 0.0f, 0.0f);
+        if (pair) {
+            if (COUNT) cnt->spheres++;
+            if (sphere_t(s1, r, tmin, RTR_INF, t)) offer(sc, best, t, RTR_MAKE_REF(REF_SPHERE, i + 1), 0.0f, 0.0f);
+        }
     } else if (VOLUMES && !NESTED && kind == REF_VOLUME) {
         const VolumeRec& vol = sc.volumes[RTR_REF_INDEX(cur)];
         float t = volume_hit(sc, vol, r, inv, tmin, RTR_INF, key, stack.nested(sp), EXHAUSTIVE, COUNT ? cnt : nullptr);
