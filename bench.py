@@ -251,6 +251,9 @@ def main():
     lowered = scene.lower()
     pe = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel)
     e2e_steps = max(1, min(args.steps, 3))
+    ds = ctx.upload(lowered)  # one untimed warm-up pass of the same call sequence (grows the library's memory pool once)
+    ds.render_into(pe, host_rgba.data_ptr())
+    ds.close()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()

@@ -20,5 +20,5 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/final_launches_mesh_hdri.csv python bench.py --workload mesh_hdri --spp 16 --steps 2 --warmup 1 --no-cpu > gpurun_out/final_ncu_mesh.log 2>&1
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:render_scan -s 1 -c 1 -f -o gpurun_out/final_prof_benchmark_scan python bench.py --steps 1 --warmup 1 --no-cpu --spp 128 > gpurun_out/final_prof_scan.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:wf_(extend|shade)' -s 24 -c 12 -f -o gpurun_out/final_prof_mesh_wave python bench.py --workload mesh_hdri --spp 16 --steps 1 --warmup 1 --no-cpu > gpurun_out/final_prof_mesh.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:wf_extend' -s 24 -c 2 -f -o gpurun_out/final_prof_volumes_extend python bench.py --workload volumes --spp 16 --steps 1 --warmup 1 --no-cpu > gpurun_out/final_prof_volumes.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k 'regex:wf_extend' -s 32 -c 3 -f -o gpurun_out/final_prof_volumes_extend python bench.py --workload volumes --spp 16 --steps 1 --warmup 1 --no-cpu > gpurun_out/final_prof_volumes.log 2>&1
 tail -3 gpurun_out/final_pytest.txt
