@@ -446,7 +446,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
         const uint64_t cap = (uint64_t)ctx->sm_count * cap_per_sm;
         return (int)(b < 1 ? 1 : b > cap ? cap : b);
     };
-    const int ext_grid = blocks_for(n_paths, per_sm);
+    const int ext_grid = blocks_for(n_paths * RTR_WF_THREADS / RTR_WF_EXTEND_THREADS, per_sm);
     const int gen_grid = blocks_for(n_paths + 32 * (uint64_t)ws * (W / 8 + H / 4 + 2), 16);
     const int shade_grid = blocks_for(n_paths, 16);
     const int sum_grid = blocks_for(n_pixels, 8);

@@ -88,6 +88,9 @@ cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, u
 // Path state lives in HBM as SoA float4 streams, double-buffered so that wf_shade writes the
 // surviving paths DENSELY (warp ballot + popc + one atomic per warp) into the other buffer.
 #define RTR_WF_THREADS 128
+#ifndef RTR_WF_EXTEND_THREADS
+#define RTR_WF_EXTEND_THREADS 128  // CTA size of wf_extend (swept 64 / 128 / 256 on B200)
+#endif
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS
 #define RTR_WF_EXTEND_MIN_BLOCKS 8  // wf_extend with Volume::hit compiled in (64 registers)
 #endif

@@ -102,10 +102,10 @@ __global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArg
 // non-inlined call with two nested walks; compiling it out of the walk removes the call's register save/restore
 // and the per-ray RNG key from the traversal state (ncu: local-memory traffic was 44 % of wf_extend's L1 wavefronts).
 template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES>
-__global__ void __launch_bounds__(RTR_WF_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL) wf_extend_kernel(const WfArgs a) {
+__global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL) wf_extend_kernel(const WfArgs a) {
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
-    __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_THREADS];
-    ShortStack<RTR_SHORT_STACK, RTR_WF_THREADS> wstack;
+    __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_EXTEND_THREADS];
+    ShortStack<RTR_SHORT_STACK, RTR_WF_EXTEND_THREADS> wstack;
     wstack.sh = &short_stack[0][threadIdx.x];
     wstack.loc = stack;
     const uint32_t FULL = 0xffffffffu;
@@ -370,7 +370,7 @@ static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, F f) {
 int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes) {
     int n = 0;
     cudaError_t e = pick_wf_extend(exhaustive, count, volumes, [&](void (*k)(const WfArgs)) {
-        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_WF_THREADS, 0);
+        return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_WF_EXTEND_THREADS, 0);
     });
     return e == cudaSuccess ? n : 0;
 }
@@ -390,7 +390,7 @@ cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool co
     // the generic instantiation also carries the BVH-off linear scan
     const bool volumes = a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u;
     pick_wf_extend(exhaustive, count, volumes, [&](void (*k)(const WfArgs)) {
-        k<<<grid, RTR_WF_THREADS, 0, st>>>(a);
+        k<<<grid, RTR_WF_EXTEND_THREADS, 0, st>>>(a);
         return cudaSuccess;
     });
     return cudaGetLastError();
