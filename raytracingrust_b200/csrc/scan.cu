@@ -108,13 +108,18 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
                             const v3 att = kind == RTR_MAT_DIELECTRIC ? mk(1.0f, 1.0f, 1.0f) : color;
                             L = (T * att) * mk(0.0f, 0.0f, 0.0f);
                             fin = true;
-                        } else if (kind == RTR_MAT_DIELECTRIC) {  // prologue, materials.rs:114-124
-                            ratio = front_face ? 1.0f / param : param;
-                            unit = normalize(ray.d);
-                            cos_theta = fminf(dot(normal, -unit), 1.0f);
-                            const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
-                            cannot_refract = (ratio * sin_theta) > 1.0f;
-                            want = cannot_refract ? W_NONE : W_UNIFORM;  // no draw under total internal reflection (Q11)
+                        } else if (kind == RTR_MAT_DIELECTRIC || kind == RTR_MAT_METAL) {
+                            // one normalize site for both: the Dielectric's unit direction (materials.rs:120) and the
+                            // Metal's unit reflection (:59); a normalize is ~25 instructions with IEEE sqrt and division
+                            unit = normalize(kind == RTR_MAT_METAL ? reflect(ray.d, normal) : ray.d);
+                            want = W_BALL;
+                            if (kind == RTR_MAT_DIELECTRIC) {  // prologue, materials.rs:114-124
+                                ratio = front_face ? 1.0f / param : param;
+                                cos_theta = fminf(dot(normal, -unit), 1.0f);
+                                const float sin_theta = sqrtf(1.0f - cos_theta * cos_theta);
+                                cannot_refract = (ratio * sin_theta) > 1.0f;
+                                want = cannot_refract ? W_NONE : W_UNIFORM;  // no draw under total internal reflection (Q11)
+                            }
                         } else {
                             want = W_BALL;  // Lambertian / Metal / Isotropic
                         }
@@ -163,12 +168,13 @@ __global__ void __launch_bounds__(RTR_MEGA_THREADS, RTR_SCAN_MIN_BLOCKS) render_
             } else if (alive) {  // Material::scatter, second half  [bucket:scatter]
                 bool some = true;
                 v3 att = color, dir;
+                v3 nball = ball;  // unit_sphere_surface() of Lambertian and Metal (sample.rs:66-70), one site for both
+                if (kind == RTR_MAT_LAMBERTIAN || kind == RTR_MAT_METAL) nball = normalize(ball);
                 if (kind == RTR_MAT_LAMBERTIAN) {  // materials.rs:31-41
-                    dir = normal + normalize(ball);
+                    dir = normal + nball;
                     if (near_zero(dir)) dir = normal;
                 } else if (kind == RTR_MAT_METAL) {  // :58-70
-                    const v3 reflected = normalize(reflect(ray.d, normal));
-                    dir = reflected + param * normalize(ball);
+                    dir = unit + param * nball;
                     some = dot(dir, normal) > 0.0f;
                     if (!some) att = mk(0.0f, 0.0f, 0.0f);
                 } else if (kind == RTR_MAT_DIELECTRIC) {  // :125-138
