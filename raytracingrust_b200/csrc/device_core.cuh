@@ -604,9 +604,11 @@ __device__ __forceinline__ ScatterPrep scatter_prepare(const SceneView& sc, bool
     p.ratio = 1.0f; p.cos_theta = 0.0f;
     p.unit = mk(0.0f, 0.0f, 0.0f);
     p.cannot_refract = false;
+    // one normalize site for the Dielectric's unit direction (:120) and the Metal's unit reflection (:59)
+    if (p.kind == RTR_MAT_DIELECTRIC || p.kind == RTR_MAT_METAL)
+        p.unit = normalize(p.kind == RTR_MAT_METAL ? reflect(ray.d, hit.normal) : ray.d);
     if (p.kind == RTR_MAT_DIELECTRIC) {
         p.ratio = hit.front_face ? 1.0f / p.param : p.param;
-        p.unit = normalize(ray.d);
         p.cos_theta = fminf(dot(hit.normal, -p.unit), 1.0f);
         const float sin_theta = sqrtf(1.0f - p.cos_theta * p.cos_theta);
         p.cannot_refract = (p.ratio * sin_theta) > 1.0f;
@@ -621,13 +623,14 @@ __device__ __forceinline__ Scatter scatter_finish(const ScatterPrep& p, v3 ball,
     s.ray.d = mk(0.0f, 0.0f, 0.0f);
     s.attenuation = p.color;
     s.some = true;
+    v3 nball = ball;  // unit_sphere_surface() of Lambertian and Metal (sample.rs:66-70): one normalize site for both
+    if (p.kind == RTR_MAT_LAMBERTIAN || p.kind == RTR_MAT_METAL) nball = normalize(ball);
     if (p.kind == RTR_MAT_LAMBERTIAN) {  // materials.rs:31-41
-        v3 dir = hit.normal + normalize(ball);
+        v3 dir = hit.normal + nball;
         if (near_zero(dir)) dir = hit.normal;
         s.ray.d = dir;
-    } else if (p.kind == RTR_MAT_METAL) {  // :58-70
-        const v3 reflected = normalize(reflect(ray.d, hit.normal));
-        s.ray.d = reflected + p.param * normalize(ball);
+    } else if (p.kind == RTR_MAT_METAL) {  // :58-70 (p.unit = the unit reflection, scatter_prepare)
+        s.ray.d = p.unit + p.param * nball;
         s.some = dot(s.ray.d, hit.normal) > 0.0f;
         if (!s.some) s.attenuation = mk(0.0f, 0.0f, 0.0f);
     } else if (p.kind == RTR_MAT_DIELECTRIC) {  // :125-138
