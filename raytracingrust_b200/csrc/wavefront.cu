@@ -21,6 +21,9 @@
 #include "device_core.cuh"
 #include "kernels.h"
 
+#ifndef RTR_WF_SHADE_MIN_BLOCKS
+#define RTR_WF_SHADE_MIN_BLOCKS 9  // wf_shade waits on memory (ncu: 3.8 long-scoreboard stalls per issue); swept 9 / 12 / 16
+#endif
 #ifndef RTR_WF_NODE_BURST
 #define RTR_WF_NODE_BURST 0  // 1: two node steps per scheduling decision
 #endif
@@ -260,7 +263,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
 
 // ------------------------------------------------------------------ shade + compact
 template <bool COUNT>
-__global__ void __launch_bounds__(RTR_WF_THREADS) wf_shade_kernel(const WfArgs a) {
+__global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_SHADE_MIN_BLOCKS) wf_shade_kernel(const WfArgs a) {
     const uint32_t FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = a.counters[WFC_QCOUNT + a.bounce];
