@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RTR_ABI_VERSION 1u
+#define RTR_ABI_VERSION 2u
 #define RTR_NO_HIT 0xFFFFFFFFu
 
 typedef enum rtr_status {
@@ -34,8 +34,9 @@ typedef enum rtr_status {
     RTR_INVALID_ARG = 1,  /* the reference would panic (unwrap/expect/index) */
     RTR_CUDA_ERROR = 2,
     RTR_OOM = 3,
-    RTR_UNSUPPORTED = 4,  /* e.g. Volume whose boundary is another Volume */
-    RTR_IO_ERROR = 5
+    RTR_UNSUPPORTED = 4,
+    RTR_IO_ERROR = 5,
+    RTR_NCCL_ERROR = 6
 } rtr_status;
 
 /* cgmath::Vector3<f32> (lib/utils/types.rs:8) and Color (lib/utils/color.rs:6-11) */
@@ -225,6 +226,45 @@ rtr_status rtr_render_accumulate_device(rtr_context* ctx, const rtr_scene* scene
 rtr_status rtr_resolve_device(rtr_context* ctx, const float* accum_dev, uint32_t width,
                               uint32_t height, uint32_t samples_per_pixel, uint8_t* rgba8_dev);
 rtr_status rtr_synchronize(rtr_context* ctx);
+
+/* ---- one render() over N GPUs of this process -------------------------------------------------
+ * render() (lib/core/render.rs:61-127) splits its pixels over host threads with rayon (render.rs:114-119); here the
+ * SAMPLES of every pixel (render.rs:86-100) are split over the devices of a group: the scene is replicated, device r
+ * renders a contiguous slice of the call's global samples into its own W*H float4 buffer (Philox is keyed by the
+ * global (pixel, sample), so the image does not depend on N except for fp32 summation order), and ONE cross-device
+ * step follows: either ncclReduce(sum, fp32, root 0) + resolve on the root (RTR_REDUCE_NCCL), or the library's own
+ * kernel in which every device sums its 1/N of the image from all peers over NVLink in rank order and stores
+ * accumulation + RGBA8 straight into the root's buffers (RTR_REDUCE_P2P, deterministic; needs peer access between all
+ * pairs).  A Rust caller binds rtr_group_* exactly like the single-device calls. */
+typedef struct rtr_group rtr_group;
+typedef struct rtr_group_scene rtr_group_scene;
+enum { RTR_REDUCE_AUTO = 0, RTR_REDUCE_NCCL = 1, RTR_REDUCE_P2P = 2 };
+enum { RTR_SPLIT_STATIC = 0, RTR_SPLIT_DYNAMIC = 1 };
+
+/* devices: CUDA device ordinals, root first (the image is produced on devices[0]); n_devices <= 16.  reduce:
+ * RTR_REDUCE_*; AUTO = P2P when every pair of devices has peer access, else NCCL (env RTR_GROUP_REDUCE=nccl|p2p
+ * overrides AUTO).  The same ordinal may appear more than once (P2P only): the slices then time-share that device,
+ * which is how the N-way split is tested on a one-GPU box. */
+rtr_status rtr_group_create(const int* devices, uint32_t n_devices, uint32_t reduce, rtr_group** out);
+void rtr_group_destroy(rtr_group* group);
+uint32_t rtr_group_size(const rtr_group* group);
+uint32_t rtr_group_reduce_mode(const rtr_group* group); /* what AUTO resolved to */
+const char* rtr_group_last_error(const rtr_group* group);
+/* flattens ONCE on the host, then uploads to every device of the group concurrently */
+rtr_status rtr_group_scene_upload(rtr_group* group, const rtr_scene_desc* desc, rtr_group_scene** out);
+void rtr_group_scene_destroy(rtr_group_scene* scene);
+/* Same contract as rtr_render: host buffers, synchronous.  params->sample_begin/sample_count name the call's global
+ * samples; they are partitioned over the devices.  stats_out: rays/samples/work summed over the devices, device_ms =
+ * root-stream time from the start of its render to the end of the cross-device step, kernel_launches summed. */
+rtr_status rtr_group_render(rtr_group* group, const rtr_group_scene* scene, const rtr_render_params* params,
+                            uint8_t* rgba8_out, float* accum_out, rtr_stats* stats_out);
+/* per-device view of the last rtr_group_render: stats (device_ms = that device's render kernels), its sample slice */
+rtr_status rtr_group_device_stats(const rtr_group* group, uint32_t index, rtr_stats* stats_out,
+                                  uint32_t* sample_begin, uint32_t* sample_count);
+/* RTR_SPLIT_STATIC (default): balanced contiguous slices.  RTR_SPLIT_DYNAMIC: the call's samples are cut into
+ * `chunk` -sample pieces (0 = library default) that the devices' host threads pull from a shared counter, for scenes
+ * whose cost per sample differs between devices' slices (rayon's work stealing, render.rs:114-119). */
+rtr_status rtr_group_set_split(rtr_group* group, uint32_t split, uint32_t chunk);
 
 /* world.hit(ray, tmin, +INF) for explicit rays (render.rs:38).  Ray i draws any
  * volume random numbers from counter (pixel=i, sample=0, bounce=0). */

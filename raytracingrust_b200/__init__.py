@@ -8,6 +8,6 @@ from . import _abi
 from .scene import (Camera, Color, Dielectric, Emission, GradientBackground, Isotropic, Lambertian,
                     MaterialHandle, Mesh, Metal, MixMaterial, ObjectHandle, RenderMode, RenderSettings,
                     RenderTarget, Scene, SkyMap, Sphere, UniformBackground, Vec3, Volume)
-from .render import Context, DeviceScene, RtrError, make_params, render, load_obj, load_scene_json, lib, write_png, write_exr, load_image
+from .render import Context, DeviceScene, Group, GroupScene, RtrError, make_params, render, load_obj, load_scene_json, lib, write_png, write_exr, load_image
 
 __all__ = [n for n in dir() if not n.startswith("_")]

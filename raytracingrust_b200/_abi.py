@@ -5,11 +5,12 @@ against a C probe compiled from the header.
 """
 import ctypes as C
 
-RTR_ABI_VERSION = 1
+RTR_ABI_VERSION = 2
 RTR_NO_HIT = 0xFFFFFFFF
 
-RTR_OK, RTR_INVALID_ARG, RTR_CUDA_ERROR, RTR_OOM, RTR_UNSUPPORTED, RTR_IO_ERROR = range(6)
-STATUS_NAMES = ["RTR_OK", "RTR_INVALID_ARG", "RTR_CUDA_ERROR", "RTR_OOM", "RTR_UNSUPPORTED", "RTR_IO_ERROR"]
+RTR_OK, RTR_INVALID_ARG, RTR_CUDA_ERROR, RTR_OOM, RTR_UNSUPPORTED, RTR_IO_ERROR, RTR_NCCL_ERROR = range(7)
+STATUS_NAMES = ["RTR_OK", "RTR_INVALID_ARG", "RTR_CUDA_ERROR", "RTR_OOM", "RTR_UNSUPPORTED", "RTR_IO_ERROR",
+                "RTR_NCCL_ERROR"]
 
 MODE_FULL, MODE_CLAY, MODE_RANDOM, MODE_NORMAL = range(4)
 OBJ_SPHERE, OBJ_MESH, OBJ_VOLUME = range(3)
@@ -20,6 +21,8 @@ FLAG_EXHAUSTIVE = 1
 FLAG_COUNT_WORK = 2
 FLAG_REFERENCE_TREE = 4
 FLAG_ACCUMULATE = 8
+REDUCE_AUTO, REDUCE_NCCL, REDUCE_P2P = range(3)
+SPLIT_STATIC, SPLIT_DYNAMIC = range(2)
 
 f32, u32, u64, f64 = C.c_float, C.c_uint32, C.c_uint64, C.c_double
 
@@ -138,6 +141,9 @@ EXPORTED_SYMBOLS = [
     "rtr_scene_upload", "rtr_scene_destroy", "rtr_scene_info", "rtr_render",
     "rtr_render_accumulate_device", "rtr_resolve_device", "rtr_synchronize",
     "rtr_trace_batch", "rtr_scatter_batch", "rtr_background_batch", "rtr_camera_rays",
+    "rtr_group_create", "rtr_group_destroy", "rtr_group_size", "rtr_group_reduce_mode", "rtr_group_last_error",
+    "rtr_group_scene_upload", "rtr_group_scene_destroy", "rtr_group_render", "rtr_group_device_stats",
+    "rtr_group_set_split",
     "rtr_scene_load_json", "rtr_host_scene_desc", "rtr_host_scene_camera", "rtr_host_scene_settings",
     "rtr_host_scene_destroy", "rtr_mesh_load_obj", "rtr_host_mesh_get", "rtr_host_mesh_destroy",
     "rtr_write_png", "rtr_write_exr", "rtr_image_load", "rtr_host_image_width", "rtr_host_image_height",

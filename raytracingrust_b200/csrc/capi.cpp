@@ -14,6 +14,7 @@
 
 #include "../../include/rtr.h"
 #include "bvh_build.h"
+#include "context.h"
 #include "host_flatten.h"
 #include "kernels.h"
 
@@ -22,71 +23,19 @@ using namespace rtr;
 static std::string g_last_error;
 static std::mutex g_err_mu;
 
-struct rtr_context {
-    int device = 0;
-    cudaStream_t stream = nullptr;
-    bool own_stream = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    int sm_count = 0;
-    // scene arrays and build scratch come from this stream-ordered pool (release threshold: never): a scene upload is
-    // ~30 allocations, and plain cudaMalloc / cudaFree stalled for 0.3-0.6 s at random while multi-GB buffers were live
-    cudaMemPool_t pool = nullptr;
-    uint32_t refill_threshold = 12;  // tuning knob (RTR_REFILL_THRESHOLD), see DESIGN.md
-    uint32_t* work_counter = nullptr;
-    unsigned long long* stats = nullptr;  // STAT_COUNT
-    // scratch, grown on demand
-    float4* accum = nullptr; size_t accum_pixels = 0;
-    float4* partials = nullptr; size_t partials_elems = 0;
-    uchar4* rgba = nullptr; size_t rgba_pixels = 0;
-    float4* wf_state = nullptr; size_t wf_state_elems = 0;  // wavefront: 7 path streams (+ lbuf), see render_wavefront
-    uint32_t* wf_counters = nullptr;
-    uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
-    uint64_t wf_target_paths = 1ull << 24;  // RTR_WF_PATHS: paths in flight per wave (swept 2^22..2^25 on B200; 2.1 GB of path state)
-    int wf_use_graph = 1;  // RTR_WF_GRAPH
-    int use_scan_kernel = 1;  // RTR_SCAN_KERNEL: 0 sends all-sphere BVH-off renders through the generic megakernel
-    char* batch_in = nullptr; size_t batch_in_bytes = 0;
-    char* batch_in2 = nullptr; size_t batch_in2_bytes = 0;
-    char* batch_out = nullptr; size_t batch_out_bytes = 0;
-    std::string error;
-};
-
-struct rtr_scene {
-    rtr_context* ctx = nullptr;
-    SceneView view;
-    std::vector<void*> allocs;
-    uint64_t device_bytes = 0, h2d_bytes = 0;
-    double build_ms = 0.0;
-    uint32_t n_nodes = 0, max_depth = 0;
-    uint32_t root_entry_reference = 0xFFFFFFFFu;
-    bool built_on_device = false;
-};
-
-static rtr_status fail(rtr_context* ctx, rtr_status st, const std::string& msg) {
+namespace rtr {
+rtr_status fail(rtr_context* ctx, rtr_status st, const std::string& msg) {
     if (ctx) ctx->error = msg;
     std::lock_guard<std::mutex> lk(g_err_mu);
     g_last_error = msg;
     return st;
 }
-namespace rtr { void set_global_error(const std::string& m) { fail(nullptr, RTR_OK, m); } }
-static rtr_status cuda_fail(rtr_context* ctx, cudaError_t e, const char* what) {
+void set_global_error(const std::string& m) { fail(nullptr, RTR_OK, m); }
+rtr_status cuda_fail(rtr_context* ctx, cudaError_t e, const char* what) {
     return fail(ctx, e == cudaErrorMemoryAllocation ? RTR_OOM : RTR_CUDA_ERROR,
                 std::string(what) + ": " + cudaGetErrorString(e));
 }
-#define CU(call)                                                  \
-    do {                                                          \
-        cudaError_t e_ = (call);                                  \
-        if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call);  \
-    } while (0)
-
-template <typename T>
-static cudaError_t grow(T** p, size_t* have, size_t want) {
-    if (*have >= want && *p) return cudaSuccess;
-    if (*p) cudaFree(*p);
-    *p = nullptr; *have = 0;
-    cudaError_t e = cudaMalloc((void**)p, want * sizeof(T));
-    if (e == cudaSuccess) *have = want;
-    return e;
-}
+}  // namespace rtr
 
 // ------------------------------------------------------------------ camera (camera.rs:37-56)
 // host f32 arithmetic in the reference's order (this TU is built with -ffp-contract=off)
@@ -126,20 +75,14 @@ uint32_t rtr_abi_version(void) { return RTR_ABI_VERSION; }
 
 const char* rtr_last_error(const rtr_context* ctx) {
     if (ctx) return ctx->error.c_str();
-    return g_last_error.c_str();
+    // a per-thread copy: another thread's failure may reallocate the global string while the caller reads this one
+    static thread_local std::string copy;
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    copy = g_last_error;
+    return copy.c_str();
 }
 
-rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
-    if (!out) return fail(nullptr, RTR_INVALID_ARG, "rtr_context_create: out is NULL");
-    *out = nullptr;
-    int n = 0;
-    cudaError_t e = cudaGetDeviceCount(&n);
-    if (e != cudaSuccess || n == 0)
-        return fail(nullptr, RTR_CUDA_ERROR, std::string("no CUDA device: ") + cudaGetErrorString(e) +
-                                                 " (this library has no CPU fallback)");
-    if (device < 0 || device >= n) return fail(nullptr, RTR_INVALID_ARG, "rtr_context_create: bad device index");
-    rtr_context* ctx = new (std::nothrow) rtr_context();
-    if (!ctx) return fail(nullptr, RTR_OOM, "host allocation failed");
+static rtr_status context_init(rtr_context* ctx, int device, void* stream) {
     ctx->device = device;
     CU(cudaSetDevice(device));
     if (stream) { ctx->stream = (cudaStream_t)stream; ctx->own_stream = false; }
@@ -175,6 +118,26 @@ rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->wf_counters, WFC_WORDS * sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->stats, STAT_COUNT * sizeof(unsigned long long)));
+    return RTR_OK;
+}
+
+rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
+    if (!out) return fail(nullptr, RTR_INVALID_ARG, "rtr_context_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return fail(nullptr, RTR_CUDA_ERROR, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                                 " (this library has no CPU fallback)");
+    if (device < 0 || device >= n) return fail(nullptr, RTR_INVALID_ARG, "rtr_context_create: bad device index");
+    rtr_context* ctx = new (std::nothrow) rtr_context();
+    if (!ctx) return fail(nullptr, RTR_OOM, "host allocation failed");
+    const rtr_status st = context_init(ctx, device, stream);
+    if (st != RTR_OK) {  // release whatever was created before the failing call; the message stays in the global slot
+        (void)cudaGetLastError();
+        rtr_context_destroy(ctx);
+        return st;
+    }
     *out = ctx;
     return RTR_OK;
 }
@@ -182,14 +145,14 @@ rtr_status rtr_context_create(int device, void* stream, rtr_context** out) {
 void rtr_context_destroy(rtr_context* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->wf_state); cudaFree(ctx->wf_counters);
     cudaFree(ctx->work_counter); cudaFree(ctx->stats); cudaFree(ctx->accum); cudaFree(ctx->partials);
     cudaFree(ctx->rgba); cudaFree(ctx->batch_in); cudaFree(ctx->batch_in2); cudaFree(ctx->batch_out);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
@@ -221,42 +184,62 @@ static cudaError_t upload(rtr_scene* s, const std::vector<T>& v, const T** dst, 
     return e;
 }
 
-extern "C" {
+namespace rtr {
 
-rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_scene** out) {
-    if (!ctx || !desc || !out) return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: null argument");
-    *out = nullptr;
-    CU(cudaSetDevice(ctx->device));
+// Traversal-stack budget per thread (device_core.cuh RTR_STACK_CAP): scene levels + the deepest volume-boundary tree.
+// The traversal tree is a depth-capped SAH tree (host_flatten.cpp: balanced depth + `slack` levels); when a scene
+// would not fit the stack with the default slack it is flattened again with slack 0 — every collection then has
+// its minimal depth ceil(log2 n) + 1, and with 29-bit primitive indices three nested collections (scene, mesh,
+// volume boundary) always fit.  The reference recurses without a limit (bvh.rs:146-173).
+static uint32_t stack_limit() {
+    uint32_t lim = 96;  // == RTR_STACK_CAP
+    if (const char* e = std::getenv("RTR_STACK_LIMIT")) {  // tests lower it to exercise the re-flatten path
+        const int v = std::atoi(e);
+        if (v >= 4 && v < 96) lim = (uint32_t)v;
+    }
+    return lim;
+}
+
+rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedScene& out) {
     auto t0 = std::chrono::steady_clock::now();
     // Sphere scenes can have their BVH built on the device (bvh_build.cu): RTR_BVH_BUILD = host | device | auto
     // (auto: from 2048 objects up, where the level-by-level launches beat the host's recursive sort).
-    bool on_device = false;
     {
         const char* mode = std::getenv("RTR_BVH_BUILD");
         const bool applies = device_build_applies(*desc);
-        if (mode && std::strcmp(mode, "device") == 0) on_device = applies;
-        else if (mode && std::strcmp(mode, "host") == 0) on_device = false;
-        else on_device = applies && desc->n_objects >= 2048;
+        if (mode && std::strcmp(mode, "device") == 0) out.on_device = applies;
+        else if (mode && std::strcmp(mode, "host") == 0) out.on_device = false;
+        else out.on_device = applies && desc->n_objects >= 2048;
     }
     rtr_scene_desc host_desc = *desc;
-    if (on_device) { host_desc.objects = nullptr; host_desc.n_objects = 0; }  // materials / background still flatten on the host
-    HostFlat flat;
-    std::string err;
-    int rc = RTR_OK;
-    try {
-        rc = flatten_scene(host_desc, flat, err);
-    } catch (const std::bad_alloc&) {
-        return fail(ctx, RTR_OOM, "host allocation failed while flattening");
+    if (out.on_device) { host_desc.objects = nullptr; host_desc.n_objects = 0; }  // materials / background still flatten on the host
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        out.flat = HostFlat();
+        std::string err;
+        int rc = RTR_OK;
+        try {
+            rc = flatten_scene(host_desc, out.flat, err, attempt == 0 ? 8u : 0u);
+        } catch (const std::bad_alloc&) {
+            return fail(ctx, RTR_OOM, "host allocation failed while flattening");
+        }
+        if (rc != RTR_OK) return fail(ctx, (rtr_status)rc, "rtr_scene_upload: " + err);
+        const uint32_t need = out.flat.max_depth + out.flat.max_boundary_depth + 4;  // + the suspended outer hit and t1 of a volume query (wavefront.cu)
+        if (need <= stack_limit()) break;
+        if (attempt == 1) return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack even when balanced");
     }
-    if (rc != RTR_OK) return fail(ctx, (rtr_status)rc, "rtr_scene_upload: " + err);
-    const uint32_t need = flat.max_depth + flat.max_boundary_depth + 2;
-    if (need > 48)  // RTR_STACK_CAP
-        return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack");
-    auto t1 = std::chrono::steady_clock::now();
+    out.host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return RTR_OK;
+}
+
+rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const PreparedScene& prep, rtr_scene** out) {
+    *out = nullptr;
+    CU(cudaSetDevice(ctx->device));
+    auto t0 = std::chrono::steady_clock::now();
+    const HostFlat& flat = prep.flat;
+    const bool on_device = prep.on_device;
     rtr_scene* s = new (std::nothrow) rtr_scene();
     if (!s) return fail(ctx, RTR_OOM, "host allocation failed");
     s->ctx = ctx;
-    s->build_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
     s->n_nodes = (uint32_t)(flat.nodes.size() / 4);
     s->max_depth = flat.max_depth;
     SceneView& v = s->view;
@@ -322,7 +305,7 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
         cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, ctx->pool, &bvh, s->allocs);
         if (be != cudaSuccess) { rtr_scene_destroy(s); return cuda_fail(ctx, be, "device BVH build"); }
         if (bvh.nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
-        if (bvh.max_depth + 2 > 48) { rtr_scene_destroy(s); return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack"); }
+        if (bvh.max_depth + 2 > stack_limit()) { rtr_scene_destroy(s); return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack"); }
         v.nodes = bvh.nodes; v.spheres = bvh.spheres; v.sphere_info = bvh.sphere_info; v.objects = bvh.objects;
         v.linear_spheres = bvh.linear_spheres;
         v.root_entry = bvh.root_entry; s->root_entry_reference = bvh.root_entry;
@@ -331,9 +314,22 @@ rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_sc
         s->device_bytes += bvh.device_bytes; s->h2d_bytes += bvh.h2d_bytes;
         s->built_on_device = true;
     }
-    s->build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    s->build_ms = prep.host_ms + std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     *out = s;
     return RTR_OK;
+}
+
+}  // namespace rtr
+
+extern "C" {
+
+rtr_status rtr_scene_upload(rtr_context* ctx, const rtr_scene_desc* desc, rtr_scene** out) {
+    if (!ctx || !desc || !out) return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: null argument");
+    *out = nullptr;
+    PreparedScene prep;
+    const rtr_status st = prepare_scene(ctx, desc, prep);
+    if (st != RTR_OK) return st;
+    return upload_prepared(ctx, desc, prep, out);
 }
 
 void rtr_scene_destroy(rtr_scene* s) {
@@ -357,6 +353,8 @@ rtr_status rtr_scene_info(const rtr_scene* s, uint64_t* device_bytes, uint64_t* 
     return RTR_OK;
 }
 
+}  // extern "C"
+
 // the scene as a launch sees it: traversal tree by default, the reference topology on request
 static SceneView view_for(const rtr_scene* scene, uint32_t flags) {
     SceneView v = scene->view;
@@ -365,7 +363,7 @@ static SceneView view_for(const rtr_scene* scene, uint32_t flags) {
 }
 
 // ------------------------------------------------------------------ render
-static rtr_status check_render_args(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p) {
+rtr_status rtr::check_render_args(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p) {
     if (!ctx || !scene || !p) return fail(ctx, RTR_INVALID_ARG, "render: null argument");
     if (scene->ctx != ctx) return fail(ctx, RTR_INVALID_ARG, "render: scene belongs to another context");
     if (p->settings.max_ray_depth > 255) return fail(ctx, RTR_INVALID_ARG, "max_ray_depth is a u8 in the reference");
@@ -381,7 +379,7 @@ static rtr_status check_render_args(rtr_context* ctx, const rtr_scene* scene, co
 // ------------------------------------------------------------------ wavefront variant (wavefront.cu)
 // One wave = generate, max_ray_depth x [extend, shade+compact], ordered sample sum, next-wave bookkeeping.
 // Every queue size lives on the device, so the launch sequence of a wave is fixed: it is captured into a
-// CUDA graph once per call and replayed for each wave (falls back to plain launches if capture fails).
+// CUDA graph once per call and replayed for each wave (plain launches when capture or instantiation fails).
 static cudaError_t wf_launch_wave(rtr_context* ctx, WfArgs a, const WfPaths buf[2], bool exhaustive, bool count_work,
                                   int gen_grid, int ext_grid, int shade_grid, int sum_grid, uint32_t* launches) {
     cudaError_t e = cudaSuccess;
@@ -399,7 +397,7 @@ static cudaError_t wf_launch_wave(rtr_context* ctx, WfArgs a, const WfPaths buf[
 }
 
 static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
-                                   float4* accum_dev, bool timed, rtr_stats* stats_out) {
+                                   float4* accum_dev, bool timed, rtr_stats* stats_out, bool reset_stats) {
     const uint32_t W = p->width, H = p->height;
     const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
     const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;
@@ -450,7 +448,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     const int gen_grid = blocks_for(n_paths + 32 * (uint64_t)ws * (W / 8 + H / 4 + 2), 16);
     const int shade_grid = blocks_for(n_paths, 16);
     const int sum_grid = blocks_for(n_pixels, 8);
-    CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
+    if (reset_stats) CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
     uint32_t launches = 0;
     if (timed) CU(cudaEventRecord(ctx->ev0, ctx->stream));
     CU(launch_wf_begin(a, ctx->stream));
@@ -463,22 +461,24 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
         cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
         if (e == cudaSuccess) {
             cudaError_t le = wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, &per_wave);
-            e = cudaStreamEndCapture(ctx->stream, &graph);
+            e = cudaStreamEndCapture(ctx->stream, &graph);  // always ends the capture, also after a failed launch
             if (e == cudaSuccess && le != cudaSuccess) e = le;
         }
         if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
         if (e == cudaSuccess) {
+            // from here on work is in flight: a failing launch is an error, not a reason to start over
             for (uint32_t w = 0; w < n_waves && e == cudaSuccess; ++w) e = cudaGraphLaunch(exec, ctx->stream);
+            if (exec) cudaGraphExecDestroy(exec);
+            if (graph) cudaGraphDestroy(graph);
+            if (e != cudaSuccess) return cuda_fail(ctx, e, "wavefront graph launch");
             launches += per_wave * n_waves;
-            done = e == cudaSuccess;
-        }
-        if (exec) cudaGraphExecDestroy(exec);
-        if (graph) cudaGraphDestroy(graph);
-        if (!done) {
+            done = true;
+        } else {
+            // capture / instantiation is unavailable here (e.g. the caller's stream is itself being captured): nothing
+            // has run yet, so clear the error and issue the same sequence as plain launches below
+            if (exec) cudaGraphExecDestroy(exec);
+            if (graph) cudaGraphDestroy(graph);
             (void)cudaGetLastError();
-            if (e != cudaSuccess && e != cudaErrorStreamCaptureUnsupported && e != cudaErrorNotSupported)
-                return cuda_fail(ctx, e, "wavefront graph");
-            return fail(ctx, RTR_CUDA_ERROR, "wavefront: CUDA graph capture unavailable on this stream (set RTR_WF_GRAPH=0)");
         }
     }
     if (!done)
@@ -495,8 +495,8 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
 }
 
 // launches the render kernels for this call's sample slice into accum_dev; fills stats (async)
-static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
-                              float4* accum_dev, bool timed, rtr_stats* stats_out) {
+rtr_status rtr::render_into(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p,
+                            float4* accum_dev, bool timed, rtr_stats* stats_out, bool reset_stats) {
     // RTR_KERNEL_AUTO (measured on B200, DESIGN.md "Megakernel or wavefront"): a BVH walk whose length varies
     // from ray to ray is where the wavefront's cheap lane refill pays for its path-state traffic; the linear
     // scan (BVH off), tiny trees and renders too small to fill a wave stay in the single-launch megakernel.
@@ -506,7 +506,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
         const bool wf = p->settings.enable_bvh_tree != 0 && scene->n_nodes >= 64 && paths >= (1ull << 20);
         kernel = wf ? RTR_KERNEL_WAVEFRONT : RTR_KERNEL_MEGAKERNEL;
     }
-    if (kernel == RTR_KERNEL_WAVEFRONT) return render_wavefront(ctx, scene, p, accum_dev, timed, stats_out);
+    if (kernel == RTR_KERNEL_WAVEFRONT) return render_wavefront(ctx, scene, p, accum_dev, timed, stats_out, reset_stats);
     const uint32_t W = p->width, H = p->height;
     const uint32_t count = p->sample_count ? p->sample_count : p->settings.samples_per_pixel;
     const bool exhaustive = (p->flags & RTR_FLAG_EXHAUSTIVE) != 0;
@@ -551,7 +551,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     a.work_counter = ctx->work_counter;
     a.stats = ctx->stats;
     CU(cudaMemsetAsync(ctx->work_counter, 0, sizeof(uint32_t), ctx->stream));
-    CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
+    if (reset_stats) CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
     uint32_t launches = 0;
     if (timed) CU(cudaEventRecord(ctx->ev0, ctx->stream));
     if (W && H) {
@@ -577,7 +577,7 @@ static rtr_status render_into(rtr_context* ctx, const rtr_scene* scene, const rt
     return RTR_OK;
 }
 
-static rtr_status collect_stats(rtr_context* ctx, bool timed, rtr_stats* stats_out) {
+rtr_status rtr::collect_stats(rtr_context* ctx, bool timed, rtr_stats* stats_out) {
     if (!stats_out) return RTR_OK;
     unsigned long long h[STAT_COUNT];
     CU(cudaMemcpyAsync(h, ctx->stats, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
@@ -591,6 +591,8 @@ static rtr_status collect_stats(rtr_context* ctx, bool timed, rtr_stats* stats_o
     }
     return RTR_OK;
 }
+
+extern "C" {
 
 rtr_status rtr_render(rtr_context* ctx, const rtr_scene* scene, const rtr_render_params* p, uint8_t* rgba8_out,
                       float* accum_out, rtr_stats* stats_out) {

@@ -17,7 +17,7 @@ namespace rtr {
 
 #define RTR_INF __int_as_float(0x7f800000)
 #define RTR_PI 3.14159265358979323846f  // std::f32::consts::PI (types.rs:5)
-#define RTR_STACK_CAP 48                // (ref, enter) pairs per thread; host checks max depth
+#define RTR_STACK_CAP 96                // (ref, enter) pairs per thread; the host flattens every scene to fit (capi.cpp stack_limit)
 
 // ------------------------------------------------------------------ vectors (cgmath 0.18 order)  [bucket:vecmath]
 // struct v3 { float x, y, z; } comes from kernels.h

@@ -71,6 +71,7 @@ struct Flattener {
     const rtr_scene_desc& d;
     std::string& err;
     uint32_t rank = 0;
+    uint32_t slack = 8;  // levels the SAH traversal tree may exceed the balanced depth by (0 = always balanced)
 
     Flattener(HostFlat& o, const rtr_scene_desc& desc, std::string& e) : out(o), d(desc), err(e) {}
 
@@ -194,7 +195,7 @@ struct Flattener {
         }
         uint32_t levels = 0;
         while ((size_t(1) << levels) < n) ++levels;
-        const FastOut f = build_traversal(gated, 0, gated.size(), levels + 8);
+        const FastOut f = build_traversal(gated, 0, gated.size(), levels + slack);
         root.fast_ref = f.ref;
         root.fast_depth = f.depth;
         return root;
@@ -422,9 +423,10 @@ bool validate(const rtr_scene_desc& d, std::string& err) {
 
 }  // namespace
 
-int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err) {
+int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint32_t slack) {
     if (!validate(d, err)) return err.find("unsupported") != std::string::npos ? RTR_UNSUPPORTED : RTR_INVALID_ARG;
     Flattener f(out, d, err);
+    f.slack = slack;
     out.nodes.reserve(64);
     Flattener::SceneColl coll(f);
     std::vector<uint32_t> handles(d.n_objects);

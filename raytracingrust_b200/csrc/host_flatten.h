@@ -23,8 +23,9 @@ struct HostFlat {
     uint32_t max_boundary_depth = 0;  // deepest volume-boundary tree
 };
 
-// returns an rtr_status; on failure `err` says why
-int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err);
+// returns an rtr_status; on failure `err` says why.  `slack` = levels a collection's SAH traversal tree may exceed its
+// balanced depth ceil(log2 n) by (0: every split is the median, the minimal depth)
+int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err, uint32_t slack = 8);
 
 }  // namespace rtr
 #endif

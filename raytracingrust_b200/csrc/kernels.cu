@@ -200,6 +200,37 @@ __global__ void resolve_kernel(const float4* accum, uchar4* rgba, uint32_t n_pix
     rgba[i] = make_uchar4(f32_as_u8(r * 255.0f), f32_as_u8(g * 255.0f), f32_as_u8(b * 255.0f), 255);
 }
 
+// The cross-device step of a multi-GPU render, fused with the resolve: this device's share of the image is
+// reduced over the N accumulation buffers by 128-bit PEER loads (NVLink / NVSwitch; the local buffer is one of them),
+// summed in rank order so the result does not depend on timing, and leaves as one float4 + one uchar4 peer store into
+// the root's buffers.  Per pixel N x 16 B cross the links inbound and 20 B outbound; every device moves 1/N of the image,
+// so all NVLink ports are busy at once (a root-only gather would pull N x the image through one port).
+__global__ void __launch_bounds__(256) reduce_resolve_peers_kernel(const PeerAccum peers, uint32_t n_ranks, float4* accum_root,
+                                                                   uchar4* rgba_root, uint32_t lo, uint32_t hi, float spp) {
+    for (uint32_t p = lo + blockIdx.x * blockDim.x + threadIdx.x; p < hi; p += gridDim.x * blockDim.x) {
+        float4 v[RTR_MAX_GROUP];
+#pragma unroll
+        for (uint32_t r = 0; r < RTR_MAX_GROUP; ++r)  // all loads in flight before the first add
+            if (r < n_ranks) v[r] = __ldcv(peers.accum[r] + p);
+        float4 s = v[0];
+#pragma unroll
+        for (uint32_t r = 1; r < RTR_MAX_GROUP; ++r)
+            if (r < n_ranks) { s.x = s.x + v[r].x; s.y = s.y + v[r].y; s.z = s.z + v[r].z; s.w = s.w + v[r].w; }
+        accum_root[p] = s;
+        const float r8 = sqrtf(s.x / spp), g8 = sqrtf(s.y / spp), b8 = sqrtf(s.z / spp);  // render.rs:103-110
+        rgba_root[p] = make_uchar4(f32_as_u8(r8 * 255.0f), f32_as_u8(g8 * 255.0f), f32_as_u8(b8 * 255.0f), 255);
+    }
+}
+cudaError_t launch_reduce_resolve_peers(const PeerAccum& peers, uint32_t n_ranks, float4* accum_root, uchar4* rgba_root,
+                                        uint32_t lo, uint32_t hi, float spp, cudaStream_t st) {
+    if (hi <= lo) return cudaSuccess;
+    const uint32_t n = hi - lo;
+    uint32_t blocks = (n + 255u) / 256u;
+    if (blocks > 148u * 8u) blocks = 148u * 8u;
+    reduce_resolve_peers_kernel<<<blocks, 256, 0, st>>>(peers, n_ranks, accum_root, rgba_root, lo, hi, spp);
+    return cudaGetLastError();
+}
+
 // SkyMap.image (backgrounds.rs:59-81: RGB f32, alpha dropped) -> float4 texels, one 128-bit fetch per lookup
 __global__ void expand_env_kernel(const float* rgb, float4* out, size_t n) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)

@@ -72,6 +72,13 @@ cudaError_t launch_scan_kernel(const RenderArgs& a, int grid, bool count, cudaSt
 cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_pixels, uint32_t n_chunks, bool accumulate, cudaStream_t st);
 cudaError_t launch_expand_env(const float* rgb, float4* out, size_t n, cudaStream_t st);
 cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels, float spp, cudaStream_t st);
+// Multi-device reduce fused with the resolve (group.cpp): for the pixels [lo, hi) this device owns, sum the N devices'
+// accumulation buffers IN RANK ORDER (peer loads over NVLink), store the sum in the root's accumulation buffer and
+// sqrt(sum/spp) -> RGBA8 in the root's image (peer stores).  One launch per device, no other collective.
+#define RTR_MAX_GROUP 16
+struct PeerAccum { const float4* accum[RTR_MAX_GROUP]; };
+cudaError_t launch_reduce_resolve_peers(const PeerAccum& peers, uint32_t n_ranks, float4* accum_root, uchar4* rgba_root,
+                                        uint32_t lo, uint32_t hi, float spp, cudaStream_t st);
 cudaError_t launch_trace_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float tmin, uint32_t bvh,
                                bool exhaustive, uint32_t k0, uint32_t k1, rtr_hit* out, unsigned long long* stats,
                                cudaStream_t st);

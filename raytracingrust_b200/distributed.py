@@ -34,21 +34,35 @@ def render_distributed(accumulate, resolve, width, height, spp, group=None, dst=
 
 
 def render_distributed_gpu(ctx, dev_scene, scene, width, height, seed=0, group=None):
-    """The GPU instantiation: rtr_render_accumulate_device + NCCL reduce + rtr_resolve_device."""
+    """The GPU instantiation: rtr_render_accumulate_device + NCCL reduce + rtr_resolve_device.
+
+    Three streams can be involved: the library launches on the context's stream, torch allocates and NCCL reduces on
+    torch's current stream.  Unless the context was created ON torch's current stream (ctx.stream_handle), each step
+    is fenced from the next: the accumulation must be complete before the reduce reads it, and the reduce before the
+    resolve."""
     from .render import make_params
     spp = scene.settings.samples_per_pixel
+    shared = ctx.stream_handle is not None and ctx.stream_handle == torch.cuda.current_stream().cuda_stream
 
     def accumulate(begin, count):
         acc = torch.empty((height, width, 4), dtype=torch.float32, device="cuda")
         if count == 0:
             return acc.zero_()
+        if not shared:
+            torch.cuda.current_stream().synchronize()  # the allocation (and any earlier use of the block) is settled
         p = make_params(scene, width, height, seed=seed, sample_begin=begin, sample_count=count)
         dev_scene.render_accumulate_device(p, acc.data_ptr(), want_stats=False)
+        if not shared:
+            ctx.synchronize()  # render kernels done before NCCL (torch's stream) reads acc
         return acc
 
     def resolve(acc, n):
         rgba = torch.empty((height, width, 4), dtype=torch.uint8, device="cuda")
+        if not shared:
+            torch.cuda.current_stream().synchronize()  # the reduce has landed in acc
         ctx.resolve_device(acc.data_ptr(), width, height, n, rgba.data_ptr())
+        if not shared:
+            ctx.synchronize()  # rgba is complete before torch reads it
         return rgba
 
     return render_distributed(accumulate, resolve, width, height, spp, group)

@@ -51,6 +51,21 @@ def lib():
     L.rtr_scatter_batch.argtypes = [vp, vp, vp, sz, u32, u64, vp]
     L.rtr_background_batch.argtypes = [vp, vp, vp, sz, vp]
     L.rtr_camera_rays.argtypes = [vp, C.POINTER(A.RenderParams), vp, vp, sz, vp]
+    L.rtr_group_create.argtypes = [C.POINTER(C.c_int), u32, u32, C.POINTER(vp)]
+    L.rtr_group_destroy.argtypes = [vp]
+    L.rtr_group_destroy.restype = None
+    L.rtr_group_size.argtypes = [vp]
+    L.rtr_group_size.restype = u32
+    L.rtr_group_reduce_mode.argtypes = [vp]
+    L.rtr_group_reduce_mode.restype = u32
+    L.rtr_group_last_error.argtypes = [vp]
+    L.rtr_group_last_error.restype = C.c_char_p
+    L.rtr_group_scene_upload.argtypes = [vp, C.POINTER(A.SceneDesc), C.POINTER(vp)]
+    L.rtr_group_scene_destroy.argtypes = [vp]
+    L.rtr_group_scene_destroy.restype = None
+    L.rtr_group_render.argtypes = [vp, vp, C.POINTER(A.RenderParams), vp, vp, C.POINTER(A.Stats)]
+    L.rtr_group_device_stats.argtypes = [vp, u32, C.POINTER(A.Stats), C.POINTER(u32), C.POINTER(u32)]
+    L.rtr_group_set_split.argtypes = [vp, u32, u32]
     L.rtr_scene_load_json.argtypes = [C.c_char_p, C.POINTER(vp)]
     L.rtr_host_scene_desc.argtypes = [vp]
     L.rtr_host_scene_desc.restype = C.POINTER(A.SceneDesc)
@@ -177,6 +192,8 @@ class Context:
         self._h = C.c_void_p()
         _check(lib().rtr_context_create(device, stream, C.byref(self._h)))
         self.device = device
+        # the caller's cudaStream_t as an integer (None: the library owns a private non-blocking stream)
+        self.stream_handle = None if stream is None else (stream.value if hasattr(stream, "value") else int(stream))
 
     def close(self):
         if getattr(self, "_h", None):
@@ -267,7 +284,81 @@ class DeviceScene:
         return out
 
 
+class Group:
+    """N GPUs of this process rendering ONE image (rtr_group): the scene is replicated, the samples of every pixel are
+    split over the devices, one cross-device reduce (the library's NVLink peer kernel, or ncclReduce) + resolve."""
+
+    def __init__(self, devices, reduce=A.REDUCE_AUTO):
+        devices = list(devices)
+        arr = (C.c_int * len(devices))(*devices)
+        self._h = C.c_void_p()
+        _check(lib().rtr_group_create(arr, len(devices), reduce, C.byref(self._h)))
+        self.devices = devices
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().rtr_group_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def reduce_mode(self):
+        return {A.REDUCE_NCCL: "nccl", A.REDUCE_P2P: "p2p"}[lib().rtr_group_reduce_mode(self._h)]
+
+    def set_split(self, split, chunk=0):
+        _check(lib().rtr_group_set_split(self._h, split, chunk))
+
+    def upload(self, scene):
+        return GroupScene(self, scene)
+
+    def device_stats(self, i):
+        st, b, c = A.Stats(), C.c_uint32(), C.c_uint32()
+        _check(lib().rtr_group_device_stats(self._h, i, C.byref(st), C.byref(b), C.byref(c)))
+        d = st.as_dict()
+        d.update(sample_begin=b.value, sample_count=c.value)
+        return d
+
+
+class GroupScene:
+    """The scene flattened once and resident on every device of a Group (rtr_group_scene)."""
+
+    def __init__(self, group, scene):
+        self.group = group
+        lowered = scene.lower() if hasattr(scene, "lower") else scene
+        self._h = C.c_void_p()
+        rc = lib().rtr_group_scene_upload(group._h, C.byref(lowered.desc), C.byref(self._h))
+        if rc != A.RTR_OK:
+            raise RtrError(rc, (lib().rtr_group_last_error(group._h) or b"").decode())
+
+    def close(self):
+        if getattr(self, "_h", None) and getattr(self.group, "_h", None):
+            lib().rtr_group_scene_destroy(self._h)
+        self._h = None
+
+    __del__ = close
+
+    def _render(self, params, rgba_ptr, accum_ptr):
+        st = A.Stats()
+        rc = lib().rtr_group_render(self.group._h, self._h, C.byref(params), rgba_ptr, accum_ptr, C.byref(st))
+        if rc != A.RTR_OK:
+            raise RtrError(rc, (lib().rtr_group_last_error(self.group._h) or b"").decode())
+        return st.as_dict()
+
+    def render(self, params, want_rgba=True, want_accum=False):
+        W, H = params.width, params.height
+        rgba = np.zeros((H, W, 4), np.uint8) if want_rgba else None
+        acc = np.zeros((H, W, 4), np.float32) if want_accum else None
+        st = self._render(params, rgba.ctypes.data if want_rgba else None, acc.ctypes.data if want_accum else None)
+        return rgba, acc, st
+
+    def render_into(self, params, rgba_out, accum_out=None):
+        """Same, into caller-owned host buffers (e.g. pinned torch tensors' data_ptr)."""
+        return self._render(params, rgba_out, accum_out)
+
+
 _DEFAULT_CTX = {}
+_DEFAULT_GROUP = {}
 
 
 def default_context(device=0):
@@ -276,10 +367,25 @@ def default_context(device=0):
     return _DEFAULT_CTX[device]
 
 
-def render(target, scene, seed=0, device=0, kernel=A.KERNEL_AUTO, want_accum=False):
-    """render(&mut target, &scene) (lib/core/render.rs:61-127) on the GPU."""
+def render(target, scene, seed=0, device=0, kernel=A.KERNEL_AUTO, want_accum=False, devices=None):
+    """render(&mut target, &scene) (lib/core/render.rs:61-127) on the GPU; devices=[...] splits the samples of the
+    one image over several GPUs of this process (rtr_group_render)."""
     target.request_redraw = True  # render.rs:62
-    ctx = default_context(device)
+    if devices is not None and len(devices) > 1:
+        key = tuple(devices)
+        if key not in _DEFAULT_GROUP:
+            _DEFAULT_GROUP[key] = Group(devices)
+        gs = _DEFAULT_GROUP[key].upload(scene)  # the reference rebuilds the BVH on every call (render.rs:67)
+        try:
+            params = make_params(scene, target.width, target.height, seed=seed, kernel=kernel)
+            rgba, acc, stats = gs.render(params, want_rgba=True, want_accum=want_accum)
+        finally:
+            gs.close()
+        target.data[:] = rgba.reshape(-1)
+        target.accum = acc
+        target.stats = stats
+        return stats
+    ctx = default_context(device if devices is None else devices[0])
     dev_scene = ctx.upload(scene)  # the reference rebuilds the BVH on every call (render.rs:67)
     try:
         params = make_params(scene, target.width, target.height, seed=seed, kernel=kernel)
