@@ -1,15 +1,21 @@
 #!/usr/bin/env python
-"""bench.py — Mrays/s of the render hot path on N B200s (one process per GPU).
+"""bench.py — Mrays/s of the render hot path on N B200s (one process per GPU under torchrun).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload benchmark|simple|mesh_hdri|volumes]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--scaling strong|weak] [--no-workloads]
   python bench.py --impl reference ...     # the CPU restatement on the box's host cores
 
-A step = one render() of the workload (BASELINE.json configs[1] by default: scenes/benchmark.json
-at 1920x1080, 1024 spp).  `value` = rays/s with the scene resident in HBM (render kernels + the
-cross-rank reduce + resolve, CUDA events on the launching stream, max over ranks).  `e2e` = the
-same metric through the reference-facing call: scene upload (H2D) + render + RGBA8 D2H with host
-buffers, wall clock around synchronised calls.  N>1: every rank renders its own spp-sized sample
-slice (weak scaling), one NCCL reduce of the fp32 accumulation buffers, resolve on rank 0.
+A step = one render() of the workload.  The headline (`value`, `e2e`, `roofline`) is BASELINE.json configs[1]:
+scenes/benchmark.json at 1920x1080, 1024 spp.  The same JSON line carries a `workloads` object with one sub-record
+per other BASELINE config measured in the same run (C1 simple.json, C3 1 M-sphere BVH, C4 meshes + HDRI at 4K with
+4096 spp, C5 volumes at 1024 spp depth 16), each with its own value / ms_per_step / kernel / roofline / e2e / clocks
+(/ cpu_baseline at N=1).
+
+`value` = rays/s with the scene resident in HBM (render kernels + the cross-rank reduce + resolve, CUDA events on the
+launching stream, max over ranks).  N>1, strong scaling (default): the workload's samples are split over the ranks
+(global sample slices), ONE NCCL reduce of the fp32 accumulation buffers, resolve on rank 0 — total work is fixed.
+`e2e` = the same metric through the reference-facing call with HOST buffers: scene upload (flatten + H2D) + render +
+RGBA8 D2H.  At N>1 that call is rtr_group_render on rank 0 over all N devices (one image: upload to every device,
+render slices, the library's cross-device reduce + resolve, one D2H); the other ranks wait on a host barrier.
 """
 import argparse
 import ctypes
@@ -26,24 +32,45 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np  # noqa: E402
 
 WORKLOADS = {
-    # name: (scene recipe, W, H, spp, description)
-    "benchmark": ("benchmark", 1920, 1080, 1024, "scenes/benchmark.json 1920x1080x1024spp (5 spheres, BVH off as shipped)"),
-    "benchmark_bvh": ("benchmark_bvh", 1920, 1080, 1024, "scenes/benchmark.json with enable_bvh_tree forced on, 1920x1080x1024spp (SURVEY C2: both settings reported)"),
-    "simple": ("simple", 1920, 1080, 1024, "scenes/simple.json 1920x1080x1024spp (102 spheres, BVH on)"),
-    "mesh_hdri": ("mesh_hdri", 1920, 1080, 256, "house+plane+fancy_monkey meshes, synthetic 4096x2048 HDRI, 1920x1080x256spp"),
-    "volumes": ("volumes", 1920, 1080, 64, "mesh/sphere-bounded media over plane, synthetic HDRI, 1920x1080x64spp"),
-    "bvh_stress": ("bvh_stress", 2048, 2048, 16, "C3(ii): 1M random spheres (seed 42), pinhole 2048x2048 from (0,0,120), Lambertian, depth 6, 16spp"),
+    # name: dict(scene recipe, W, H, spp, description, BASELINE config id)
+    "benchmark": dict(W=1920, H=1080, spp=1024, config="C2",
+                      desc="scenes/benchmark.json 1920x1080x1024spp (5 spheres, BVH off as shipped)"),
+    "benchmark_bvh": dict(W=1920, H=1080, spp=1024, config="C2-bvh",
+                          desc="scenes/benchmark.json with enable_bvh_tree forced on, 1920x1080x1024spp (SURVEY C2: both settings reported)"),
+    "simple": dict(W=1920, H=1080, spp=1024, config="C1",
+                   desc="scenes/simple.json 1920x1080x1024spp (102 spheres, BVH on)"),
+    "mesh_hdri": dict(W=1920, H=1080, spp=256, config="C4-1080p",
+                      desc="house+plane+fancy_monkey meshes, synthetic 4096x2048 HDRI, 1920x1080x256spp"),
+    "mesh_hdri_4k": dict(W=3840, H=2160, spp=4096, config="C4",
+                         desc="C4: house+plane+fancy_monkey meshes, synthetic 4096x2048 HDRI, 3840x2160x4096spp split over the ranks"),
+    "volumes": dict(W=1920, H=1080, spp=64, config="C5-64spp",
+                    desc="mesh/sphere-bounded media over plane, synthetic HDRI, 1920x1080x64spp"),
+    "volumes_1024": dict(W=1920, H=1080, spp=1024, config="C5",
+                         desc="C5: mesh/sphere-bounded media over plane, synthetic 2048x1024 HDRI, 1920x1080x1024spp depth 16, strong scaling"),
+    "bvh_stress": dict(W=2048, H=2048, spp=16, config="C3",
+                       desc="C3(ii): 1M random spheres (seed 42), pinhole 2048x2048 from (0,0,120), Lambertian, depth 6, 16spp"),
+    "mesh_depth50": dict(W=1920, H=1080, spp=64, config="benches/mesh.rs",
+                         desc="benches/mesh.rs recipe at size: Dielectric(1.5) monkey, camera at the origin, depth 50, 1920x1080x64spp"),
+    "grid_depth50": dict(W=1920, H=1080, spp=16, config="benches/bvh_tree_stress.rs",
+                         desc="benches/bvh_tree_stress.rs recipe: 8000 touching glass spheres, depth 50, 1920x1080x16spp"),
 }
+# sub-records of the default run: (name, timed steps, spp cap per rank at which one step stays near 10 s, e2e spp)
+SUB_WORKLOADS = [("simple", 3, 1024, 256), ("bvh_stress", 5, 16, 16), ("mesh_hdri_4k", 1, 2048, 64),
+                 ("volumes_1024", 1, 1024, 64)]
 
 
 def make_scene(name):
     import _scenes
-    if name == "mesh_hdri":
+    if name in ("mesh_hdri", "mesh_hdri_4k"):
         return _scenes.mesh_hdri(4096, 2048)
-    if name == "volumes":
+    if name in ("volumes", "volumes_1024"):
         return _scenes.volumes(2048, 1024)
     if name == "bvh_stress":
         return _scenes.random_spheres(1_000_000)
+    if name == "mesh_depth50":
+        return _scenes.mesh_bench()
+    if name == "grid_depth50":
+        return _scenes.grid_spheres(10)
     if name == "benchmark_bvh":
         s = _scenes.benchmark()
         s.settings.enable_bvh_tree = True
@@ -102,16 +129,13 @@ class ClockSampler(threading.Thread):
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-# bounded CPU sample per workload (W, H, spp factor): the reference-shaped CPU walk tests every pierced subtree, which
-# on the 1 M-sphere scene is ~150x slower per ray than on the others — keep each sample to seconds of CPU work
+# bounded CPU sample per workload (W, H, spp): the reference-shaped CPU walk tests every pierced subtree, which on the
+# 1 M-sphere scene is ~150x slower per ray than on the others — keep each sample to seconds of CPU work
 # (16 host cores: benchmark ~6 s, simple ~4 s, mesh_hdri ~5 s, volumes ~9 s, bvh_stress ~1 s per sample)
-CPU_SAMPLE = {"bvh_stress": (256, 256, 1 / 16.0), "benchmark": (1920, 1080, 16.0), "benchmark_bvh": (1920, 1080, 16.0),
-              "simple": (1920, 1080, 4.0)}
-
-
-def cpu_sample_for(workload, W, H, spp_sample):
-    w, h, f = CPU_SAMPLE.get(workload, (W, H, 1.0))
-    return w, h, max(1, int(round(spp_sample * f)))
+CPU_SAMPLE = {"bvh_stress": (256, 256, 1), "benchmark": (1920, 1080, 256), "benchmark_bvh": (1920, 1080, 256),
+              "simple": (1920, 1080, 64), "mesh_hdri": (1920, 1080, 16), "mesh_hdri_4k": (1920, 1080, 16),
+              "volumes": (1920, 1080, 16), "volumes_1024": (1920, 1080, 16), "mesh_depth50": (1920, 1080, 16),
+              "grid_depth50": (480, 270, 4)}
 
 
 def cpu_render(scene, W, H, spp_sample, seed=0, count_work=False):
@@ -126,13 +150,24 @@ def cpu_render(scene, W, H, spp_sample, seed=0, count_work=False):
     return st
 
 
+def cpu_baseline_record(name, scene, scale=1.0):
+    cw, ch, cs = CPU_SAMPLE[name]
+    cs = max(1, int(round(cs * scale)))
+    st = cpu_render(scene, cw, ch, cs)
+    return {"value": st["rays"] / (st["device_ms"] * 1e-3) / 1e6, "unit": "Mrays/s", "cores": st["kernel_launches"],
+            "kind": "port", "msamples_per_s": st["samples"] / (st["device_ms"] * 1e-3) / 1e6,
+            "sample": f"{cw}x{ch} at {cs} spp of the workload's frame (oracle port, OpenMP over pixels, all host threads; "
+                      "rates are spp-independent)"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    name, W, H, spp, desc = WORKLOADS[args.workload]
-    scene = make_scene(name)
-    W, H, spp_sample = cpu_sample_for(args.workload, W, H, args.cpu_spp)
+    w = WORKLOADS[args.workload]
+    scene = make_scene(args.workload)
+    W, H, spp_full = CPU_SAMPLE[args.workload]
+    spp_sample = max(1, int(round(spp_full * args.cpu_spp / 16.0)))
     for _ in range(args.warmup):
         cpu_render(scene, W, H, 1)
     t_ms, rays, samples, threads = 0.0, 0, 0, 1
@@ -140,17 +175,286 @@ def run_reference(args):
         st = cpu_render(scene, W, H, spp_sample, seed=k)
         t_ms += st["device_ms"]; rays += st["rays"]; samples += st["samples"]; threads = st["kernel_launches"]
     v = rays / (t_ms * 1e-3) / 1e6
-    sample = f"{W}x{H} at {spp_sample} spp of {spp} per step (rates are spp-independent)"
-    print(json.dumps({
+    sample = f"{W}x{H} at {spp_sample} spp of {w['spp']} per step (rates are spp-independent)"
+    out = {
         "impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "msamples_per_s": samples / (t_ms * 1e-3) / 1e6,
-        "config": {"workload": desc, "note": "CPU restatement of the reference (oracle port, OpenMP over pixels); "
+        "config": {"workload": w["desc"], "note": "CPU restatement of the reference (oracle port, OpenMP over pixels); "
                    "the Rust crate cannot be built here (no cargo/rustc)"},
         "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    }
+    if not args.no_workloads and args.workload == "benchmark":
+        subs = {}
+        for name, _, _, _ in SUB_WORKLOADS:
+            rec = cpu_baseline_record(name, make_scene(name), scale=0.5)
+            subs[name] = {"config": WORKLOADS[name]["config"], "workload": WORKLOADS[name]["desc"], "value": rec["value"],
+                          "unit": "Mrays/s", "msamples_per_s": rec["msamples_per_s"], "cpu_baseline": rec}
+        out["workloads"] = subs
+    print(json.dumps(out))
+
+
+class Bench:
+    """Shared state of one bench process: torch stream, library context, process group."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        import raytracingrust_b200 as rt
+        self.args, self.torch, self.dist, self.rt = args, torch, dist, rt
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.host_group = None
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.host_group = dist.new_group(backend="gloo")  # host-side barriers: no kernel spins on a GPU
+        # a real (non-NULL) stream shared by torch (events, NCCL) and the library's launches
+        self.stream = torch.cuda.Stream()
+        torch.cuda.set_stream(self.stream)
+        self.ctx = rt.Context(self.local, stream=ctypes.c_void_p(self.stream.cuda_stream))
+        self.group = None  # rtr_group over all N devices, rank 0 only (e2e at N > 1)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        self.peak, self.peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        self.sm_count = torch.cuda.get_device_properties(self.local).multi_processor_count
+        self.counters = {}
+        try:
+            self.counters = json.load(open(os.path.join(ROOT, "profiles", "counters.json")))
+        except Exception:
+            pass
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+
+    def host_barrier(self):
+        if self.world > 1:
+            self.dist.barrier(group=self.host_group)
+
+    def reduce_pair(self, ms, rays):
+        t = self.torch.tensor([ms, float(rays)], dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            tmax = t.clone(); self.dist.all_reduce(tmax, op=self.dist.ReduceOp.MAX)
+            tsum = t.clone(); self.dist.all_reduce(tsum, op=self.dist.ReduceOp.SUM)
+            return float(tmax[0]), float(tsum[1])
+        return ms, float(rays)
+
+    def measure(self, name, steps, warmup, spp_cap=None, e2e_spp=None, warmup_spp=None, with_cpu=True):
+        """One workload: returns the record (rank 0) or None."""
+        torch, dist, rt, args = self.torch, self.dist, self.rt, self.args
+        from raytracingrust_b200 import _abi as A
+        from raytracingrust_b200.distributed import sample_slice
+        w = WORKLOADS[name]
+        W, H, spp, desc = w["W"], w["H"], w["spp"], w["desc"]
+        if args.spp and name == args.workload:
+            spp = args.spp
+            desc += f" [spp overridden to {spp}]"
+        world, rank = self.world, self.rank
+        scene = make_scene(name)
+        # the frame's samples: strong scaling splits them over the ranks, weak gives every rank the full count
+        if args.scaling == "weak":
+            total_spp, (s_begin, s_count) = spp * world, (rank * spp, spp)
+        else:
+            total_spp, (s_begin, s_count) = spp, sample_slice(spp, rank, world)
+        note = None
+        if spp_cap and s_count > spp_cap:  # keep one step near 10 s: render the first spp_cap samples of the slice
+            note = (f"per-rank slice capped at {spp_cap} of {s_count} spp so that one step stays near 10 s "
+                    f"(rates are spp-independent); image_spp counts what was rendered")
+            s_count = spp_cap
+            total_spp = spp_cap * world
+            s_begin = rank * spp_cap
+        scene.settings.samples_per_pixel = total_spp
+        dev_scene = self.ctx.upload(scene)
+        info = dev_scene.info()
+        accum = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
+        rgba = torch.empty((H, W, 4), dtype=torch.uint8, device="cuda")
+        params = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel)
+
+        def step(p=params, n=total_spp):
+            dev_scene.render_accumulate_device(p, accum.data_ptr(), want_stats=False)
+            if world > 1:
+                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)  # one NCCL reduce over NVLink
+            if rank == 0:
+                self.ctx.resolve_device(accum.data_ptr(), W, H, n, rgba.data_ptr())
+
+        # work counters (untimed, counting instantiation of the kernels) on a bounded number of samples: algorithmic
+        # work is DEFINED on the reference topology (SURVEY 8d); the traversal tree actually walked is counted too
+        c_count = min(s_count, max(1, (1 << 25) // (W * H)))
+        pc = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=c_count, kernel=args.kernel,
+                            flags=A.FLAG_COUNT_WORK | A.FLAG_REFERENCE_TREE)
+        st_ref = dev_scene.render_accumulate_device(pc, accum.data_ptr(), want_stats=True)
+        pc.flags = A.FLAG_COUNT_WORK
+        st_trav = dev_scene.render_accumulate_device(pc, accum.data_ptr(), want_stats=True)
+        w_spp = min(s_count, warmup_spp) if warmup_spp else s_count
+        pw = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=w_spp, kernel=args.kernel)
+        for _ in range(warmup):
+            step(pw, w_spp * world)
+        torch.cuda.synchronize()
+        self.barrier()
+        sampler = ClockSampler(self.local)
+        sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        ev0.record(self.stream)
+        for _ in range(steps):
+            step()
+        ev1.record(self.stream)
+        torch.cuda.synchronize()
+        self.barrier()
+        clocks = sampler.stop()
+        ms = ev0.elapsed_time(ev1)
+        # the render kernels alone (CUDA events inside the library, same stream) and the exact ray count of a step
+        kern_ms, st_full = [], None
+        for _ in range(max(1, min(steps, 3))):
+            st_full = dev_scene.render_accumulate_device(params, accum.data_ptr(), want_stats=True)
+            kern_ms.append(st_full["device_ms"])
+        # the cross-rank step alone: reduce + resolve, same buffers
+        xr_ms = 0.0
+        if world > 1:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            self.barrier(); torch.cuda.synchronize()
+            e0.record(self.stream)
+            for _ in range(5):
+                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+                if rank == 0:
+                    self.ctx.resolve_device(accum.data_ptr(), W, H, total_spp, rgba.data_ptr())
+            e1.record(self.stream)
+            torch.cuda.synchronize()
+            xr_ms = e0.elapsed_time(e1) / 5
+        k_ms = float(np.mean(kern_ms))
+        ms, rays_step = self.reduce_pair(ms, st_full["rays"])
+        k_max, _ = self.reduce_pair(k_ms, 0)
+        k_min = -self.reduce_pair(-k_ms, 0)[0]
+        xr_ms, _ = self.reduce_pair(xr_ms, 0)
+        samples_step = float(W) * H * total_spp
+
+        # ---- end to end through the reference-facing call with host buffers
+        e_spp = min(total_spp, e2e_spp) if e2e_spp else total_spp
+        scene.settings.samples_per_pixel = e_spp
+        lowered = scene.lower()
+        pe = rt.make_params(scene, W, H, seed=0, kernel=args.kernel)
+        e2e_steps = max(1, min(steps, 3))
+        e2e = None
+        dev_scene.close()
+        if world == 1:
+            host_rgba = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+            ds = self.ctx.upload(lowered)  # one untimed pass of the same call sequence (grows the library's memory pool once)
+            ds.render_into(pe, host_rgba.data_ptr()); ds.close()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            e_rays = 0
+            for _ in range(e2e_steps):
+                ds = self.ctx.upload(lowered)
+                e_rays += ds.render_into(pe, host_rgba.data_ptr())["rays"]
+                ds.close()
+            e2e_s = time.perf_counter() - t0
+            e2e = {"value": e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": info["h2d_bytes"],
+                   "d2h_bytes_per_step": W * H * 4 + 64, "steps": e2e_steps, "spp": e_spp,
+                   "call": "rtr_scene_upload + rtr_render (host RGBA8 out), wall clock"}
+        else:
+            torch.cuda.synchronize()
+            self.host_barrier()
+            if rank == 0:  # ONE image from N GPUs through one library call; the other ranks' GPUs are idle
+                if self.group is None:
+                    self.group = rt.Group(list(range(world)))
+                host_rgba = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+                gs = self.group.upload(lowered)
+                gs.render_into(pe, host_rgba.data_ptr()); gs.close()
+                t0 = time.perf_counter()
+                e_rays, g_ms, g_slow = 0, 0.0, 0.0
+                for _ in range(e2e_steps):
+                    gs = self.group.upload(lowered)
+                    st = gs.render_into(pe, host_rgba.data_ptr())
+                    e_rays += st["rays"]; g_ms += st["device_ms"]; g_slow += st["upload_ms"]
+                    gs.close()
+                e2e_s = time.perf_counter() - t0
+                e2e = {"value": e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": info["h2d_bytes"] * world,
+                       "d2h_bytes_per_step": W * H * 4 + 64, "steps": e2e_steps, "spp": e_spp,
+                       "call": f"rtr_group_scene_upload + rtr_group_render over {world} devices from rank 0 (one image; "
+                               f"cross-device step: {self.group.reduce_mode}), wall clock",
+                       "device_ms_per_step": g_ms / e2e_steps, "slowest_member_render_ms": g_slow / e2e_steps}
+            self.host_barrier()
+        if rank != 0:
+            return None
+
+        used = {1: "megakernel", 2: "wavefront"}[st_full["kernel_used"]]
+        kernel_fn = "render_megakernel" if used == "megakernel" else "wavefront wave sequence (wf_extend dominant)"
+        if (used == "megakernel" and not scene.settings.enable_bvh_tree and scene.settings.max_ray_depth >= 1
+                and os.environ.get("RTR_SCAN_KERNEL", "1") != "0" and all(isinstance(o, rt.Sphere) for o in scene.objects)):
+            used, kernel_fn = "megakernel (all-sphere scan kernel)", "render_scan_kernel"
+        # ---- roofline: algorithmic figures per ray from the counting pass x this step's rays
+        rays_rank = st_full["rays"]
+        per_ray = lambda st, f: f(st) / max(st["rays"], 1)
+        alg = per_ray(st_ref, algorithmic_bytes) * rays_rank
+        alg_trav = per_ray(st_trav, algorithmic_bytes) * rays_rank
+        ops = per_ray(st_ref, algorithmic_ops) * rays_rank
+        clock = (clocks["sm_mhz"] or 1965.0) * 1e6
+        issue_peak = self.sm_count * 4 * 32 * clock
+        achieved = alg / (k_ms * 1e-3) / 1e9
+        cnt = self.counters.get(name) or self.counters.get({"mesh_hdri_4k": "mesh_hdri", "volumes_1024": "volumes"}.get(name, ""), {}) or {}
+        traffic = cnt.get("dram_bytes_per_ray")
+        traffic_launch = traffic * rays_rank if traffic is not None else None
+        util = {"issue": cnt.get("issue_active_pct"), "l1": cnt.get("l1_lsu_wavefront_pct"), "hbm": cnt.get("dram_pct")}
+        known = {k: v for k, v in util.items() if v is not None}
+        bound = max(known, key=known.get) if known else "issue"
+        rec = {
+            "config_id": w["config"],
+            "metric": "Mrays/s", "value": rays_step * steps / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
+            "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "msamples_per_s": samples_step * steps / (ms * 1e-3) / 1e6,
+            "rays_per_step": rays_step, "samples_per_step": samples_step,
+            "config": {"workload": desc, "kernel": used, "per_gpu_spp": s_count, "image_spp": total_spp,
+                       "parallelism": f"sample-slices x{world} + ncclReduce",
+                       "l2_policy": "each step rewrites the accumulation buffer and traces fresh Philox paths; the wavefront "
+                                    "streams 2 GB of path state per wave (> the 126 MB L2); scene geometry is L2-resident by design (SURVEY 8d)",
+                       "scene_device_bytes": info["device_bytes"], "bvh_nodes": info["n_nodes"],
+                       "warmup_spp": w_spp},
+            "clocks": clocks,
+            "e2e": e2e,
+            # our kernels per step: the render kernels (megakernel, or the wavefront's per-wave sequence) + resolve_kernel
+            # (NCCL's reduce kernel is not ours)
+            "gpu_launches": steps * (st_full["kernel_launches"] + 1),
+            "per_rank": {"render_ms_max": k_max, "render_ms_min": k_min, "reduce_resolve_ms": xr_ms,
+                         "step_ms": ms / steps,
+                         "note": "render = this rank's kernels alone (library events); reduce_resolve = ncclReduce of the fp32 "
+                                 "image + resolve on rank 0, timed alone; step - render_max - reduce_resolve = launch gaps + rank skew"},
+            "roofline": {
+                "bound": bound,
+                "bound_evidence": {"smsp__issue_active_pct": util["issue"], "l1tex__data_pipe_lsu_wavefronts_pct": util["l1"],
+                                   "gpu__dram_throughput_pct": util["hbm"], "lanes_per_inst": cnt.get("lanes_per_inst"),
+                                   "source": cnt.get("source", "no ncu capture of this workload on record")},
+                "achieved": achieved, "peak": self.peak, "unit": "GB/s", "frac": achieved / self.peak,
+                "peak_source": self.peak_src, "kernel": kernel_fn, "kernel_ms": k_ms,
+                "definition": "ALGORITHMIC bytes (SURVEY 8d: 32/box + 48/triangle + 16/sphere + 16/texel + 32/ray, counted on the "
+                              "REFERENCE topology with the ordered culled walk) / kernel time: reference-equivalent work, not DRAM traffic",
+                "algorithmic_bytes_per_launch": alg, "bytes_per_ray": alg / max(rays_rank, 1),
+                "traversed": {"bytes_per_launch": alg_trav, "bytes_per_ray": alg_trav / max(rays_rank, 1),
+                              "achieved": alg_trav / (k_ms * 1e-3) / 1e9, "frac": alg_trav / (k_ms * 1e-3) / 1e9 / self.peak,
+                              "note": "the same formula counted on the traversal tree the timed kernel actually walks (binned SAH over the gate boxes, paired leaves)"},
+                "traffic": traffic_launch,
+                "traffic_note": "dram__bytes_read+write summed over every launch of a wave (ncu --set full), per ray x this step's rays; "
+                                "far below the algorithmic bytes because the scene is L2/L1-resident",
+                "hbm_frac_actual": (traffic_launch / (k_ms * 1e-3) / 1e9 / self.peak) if traffic_launch else None,
+                "l1_wavefront_frac": (util["l1"] / 100.0) if util["l1"] is not None else None,
+                "lanes_per_inst": cnt.get("lanes_per_inst"),
+                # the physically binding roofline (SURVEY 8d-2): thread-instructions
+                "issue": {"achieved": ops / (k_ms * 1e-3) / 1e12, "unit": "T thread-op/s", "peak": issue_peak / 1e12,
+                          "frac": ops / (k_ms * 1e-3) / issue_peak},
+            },
+        }
+        if note:
+            rec["config"]["note"] = note
+        if with_cpu and world == 1 and not args.no_cpu:
+            rec["cpu_baseline"] = cpu_baseline_record(name, scene, scale=args.cpu_spp / 16.0)
+        return rec
 
 
 def main():
@@ -161,174 +465,32 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="benchmark", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (debug only)")
-    ap.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU sample")
+    ap.add_argument("--cpu-spp", type=int, default=16, help="scale of the bounded CPU sample (16 = the table in CPU_SAMPLE)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-workloads", action="store_true", help="headline workload only (no `workloads` sub-records)")
     ap.add_argument("--kernel", type=int, default=0)
-    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
-                    help="weak: every rank renders the workload's spp (image has N x spp samples); strong: the workload's "
-                         "spp is split across ranks (BASELINE config 5 sweep)")
+    ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
+                    help="strong (default): the workload's spp is split across ranks, total work fixed; weak: every rank renders "
+                         "the workload's spp (image has N x spp samples)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
 
-    import torch
-    import torch.distributed as dist
-    import raytracingrust_b200 as rt
-    from raytracingrust_b200 import _abi as A
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    name, W, H, spp, desc = WORKLOADS[args.workload]
-    if args.spp:
-        spp = args.spp
-        desc += f" [spp overridden to {spp}]"
-    scene = make_scene(name)
-    scene.settings.samples_per_pixel = spp
-
-    # a real (non-NULL) stream shared by torch (events, NCCL) and the library's launches
-    stream = torch.cuda.Stream()
-    torch.cuda.set_stream(stream)
-    ctx = rt.Context(local, stream=ctypes.c_void_p(stream.cuda_stream))
-    dev_scene = ctx.upload(scene)
-    info = dev_scene.info()
-    accum = torch.empty((H, W, 4), dtype=torch.float32, device="cuda")
-    rgba = torch.empty((H, W, 4), dtype=torch.uint8, device="cuda")
-    # weak scaling: rank r renders global samples [r*spp, (r+1)*spp); the image has world*spp samples.
-    # strong scaling: the image keeps spp samples, rank r renders its balanced slice of them.
-    from raytracingrust_b200.distributed import sample_slice
-    total_spp = spp * world if args.scaling == "weak" else spp
-    s_begin, s_count = (rank * spp, spp) if args.scaling == "weak" else sample_slice(spp, rank, world)
-    params = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel)
-
-    def step():
-        dev_scene.render_accumulate_device(params, accum.data_ptr(), want_stats=False)
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)  # one NCCL reduce over NVLink
-        if rank == 0:
-            ctx.resolve_device(accum.data_ptr(), W, H, total_spp, rgba.data_ptr())
-
-    # rays per step and work counters (untimed, counting variant of the kernel)
-    pc = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel,
-                        flags=A.FLAG_COUNT_WORK | A.FLAG_REFERENCE_TREE)  # algorithmic work is DEFINED on the reference topology
-    st_count = dev_scene.render_accumulate_device(pc, accum.data_ptr(), want_stats=True)
-    for _ in range(args.warmup):
-        step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    ev0.record(stream)
-    for _ in range(args.steps):
-        step()
-    ev1.record(stream)
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    clocks = sampler.stop()
-    ms = ev0.elapsed_time(ev1)
-    # dominant kernel alone (megakernel launches only), CUDA events inside the library, same stream
-    kern_ms = []
-    for _ in range(args.steps):
-        kern_ms.append(dev_scene.render_accumulate_device(params, accum.data_ptr(), want_stats=True)["device_ms"])
-    t = torch.tensor([ms, float(st_count["rays"])], dtype=torch.float64, device="cuda")
-    if world > 1:
-        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms, rays_step = float(tmax[0]), float(tsum[1])
-    else:
-        rays_step = float(t[1])
-    samples_step = float(W) * H * total_spp
-
-    # end to end through the reference-facing call: upload (H2D) + render + RGBA8 D2H, host buffers
-    host_rgba = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
-    lowered = scene.lower()
-    pe = rt.make_params(scene, W, H, seed=0, sample_begin=s_begin, sample_count=s_count, kernel=args.kernel)
-    e2e_steps = max(1, min(args.steps, 3))
-    ds = ctx.upload(lowered)  # one untimed warm-up pass of the same call sequence (grows the library's memory pool once)
-    ds.render_into(pe, host_rgba.data_ptr())
-    ds.close()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ds = ctx.upload(lowered)
-        ds.render_into(pe, host_rgba.data_ptr())
-        ds.close()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e_s = float(te[0])
-
-    # which of our kernels the megakernel selector resolved to (capi.cpp render_into): the all-sphere BVH-off scan
-    # kernel (csrc/scan.cu) when every object is a sphere and the BVH is off, as in scenes/benchmark.json
-    used = {1: "megakernel", 2: "wavefront"}[st_count["kernel_used"]]
-    kernel_fn = "render_megakernel" if used == "megakernel" else "wavefront wave sequence (wf_extend dominant)"
-    if (used == "megakernel" and not scene.settings.enable_bvh_tree and scene.settings.max_ray_depth >= 1
-            and os.environ.get("RTR_SCAN_KERNEL", "1") != "0" and all(isinstance(o, rt.Sphere) for o in scene.objects)):
-        used, kernel_fn = "megakernel (all-sphere scan kernel)", "render_scan_kernel"
-    if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
-        k_ms = float(np.mean(kern_ms))
-        sm_count = torch.cuda.get_device_properties(local).multi_processor_count
-        alg = algorithmic_bytes(st_count)
-        achieved = alg / (k_ms * 1e-3) / 1e9
-        traffic = None
-        try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
-        except Exception:
-            pass
-        out = {
-            "metric": "Mrays/s", "value": rays_step * args.steps / (ms * 1e-3) / 1e6, "unit": "Mrays/s",
-            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "msamples_per_s": samples_step * args.steps / (ms * 1e-3) / 1e6,
-            "rays_per_step": rays_step, "samples_per_step": samples_step,
-            "config": {"workload": desc, "kernel": used, "per_gpu_spp": s_count, "image_spp": total_spp, "parallelism": f"sample-slices x{world} + ncclReduce",
-                       "l2_policy": "each step rewrites the 33 MB accumulation buffer and traces fresh Philox paths; scene working set is L2-resident by design (SURVEY 8d)",
-                       "scene_device_bytes": info["device_bytes"], "bvh_nodes": info["n_nodes"]},
-            "clocks": clocks,
-            "e2e": {"value": rays_step * e2e_steps / e2e_s / 1e6, "unit": "Mrays/s",
-                    "h2d_bytes_per_step": info["h2d_bytes"], "d2h_bytes_per_step": W * H * 4 + 64, "steps": e2e_steps},
-            # our kernels per step: the render kernels (megakernel, or the wavefront's per-wave sequence) + resolve_kernel
-            # (NCCL's reduce kernel is not ours)
-            "gpu_launches": args.steps * (st_count["kernel_launches"] + 1),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src, "kernel": kernel_fn,
-                         "kernel_ms": k_ms, "algorithmic_bytes_per_launch": alg,
-                         "bytes_per_ray": alg / max(st_count["rays"], 1),
-                         "traffic_note": "dram__bytes_read+write per launch of the dominant kernel from profiles/ (ncu --set full); "
-                                         "far BELOW the algorithmic bytes because the scene is L2/L1-resident",
-                         # secondary, physically binding roofline: thread-instructions
-                         "issue": {"achieved": algorithmic_ops(st_count) / (k_ms * 1e-3) / 1e12, "unit": "T thread-op/s",
-                                   "peak": sm_count * 4 * 32 * (clocks["sm_mhz"] or 1965.0) * 1e6 / 1e12,
-                                   "frac": algorithmic_ops(st_count) / (k_ms * 1e-3) / (sm_count * 4 * 32 * (clocks["sm_mhz"] or 1965.0) * 1e6)},
-                         "note": "scene is L2-resident: the binding units are the L1 data pipe (divergent node fetches) and SM "
-                                 "issue slots under SIMT divergence, not HBM (ncu: DESIGN.md 6, profiles/)"},
-        }
-        if not args.no_cpu:
-            cw, ch, cs = cpu_sample_for(args.workload, W, H, args.cpu_spp)
-            st = cpu_render(scene, cw, ch, cs)
-            out["cpu_baseline"] = {"value": st["rays"] / (st["device_ms"] * 1e-3) / 1e6, "unit": "Mrays/s",
-                                   "cores": st["kernel_launches"], "kind": "port",
-                                   "sample": f"{cw}x{ch} at {cs} spp (oracle port, OpenMP, all host threads)"}
+    b = Bench(args)
+    out = b.measure(args.workload, args.steps, max(args.warmup, 1))
+    subs = {}
+    if not args.no_workloads and args.workload == "benchmark":
+        for name, steps, cap, e2e_spp in SUB_WORKLOADS:
+            rec = b.measure(name, steps, 3, spp_cap=cap, e2e_spp=e2e_spp, warmup_spp=max(1, min(16, (1 << 26) // (WORKLOADS[name]["W"] * WORKLOADS[name]["H"]))))
+            if rec is not None:
+                subs[name] = rec
+    if b.rank == 0:
+        out["warmup"] = args.warmup
+        if subs:
+            out["workloads"] = subs
         print(json.dumps(out))
-    if world > 1:
-        dist.destroy_process_group()
+    if b.world > 1:
+        b.dist.destroy_process_group()
 
 
 if __name__ == "__main__":
