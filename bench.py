@@ -55,8 +55,8 @@ WORKLOADS = {
                          desc="benches/bvh_tree_stress.rs recipe: 8000 touching glass spheres, depth 50, 1920x1080x16spp"),
 }
 # sub-records of the default run: (name, timed steps, spp cap per rank at which one step stays near 10 s, e2e spp)
-SUB_WORKLOADS = [("simple", 3, 1024, 256), ("bvh_stress", 5, 16, 16), ("mesh_hdri_4k", 1, 2048, 64),
-                 ("volumes_1024", 1, 1024, 64)]
+SUB_WORKLOADS = [("simple", 3, 1024, 256), ("bvh_stress", 5, 16, 16), ("mesh_hdri_4k", 1, 2048, 256),
+                 ("volumes_1024", 1, 1024, 128)]
 
 
 def make_scene(name):

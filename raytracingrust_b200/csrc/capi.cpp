@@ -2,6 +2,7 @@
 //
 // No CPU fallback exists: every entry point that computes launches CUDA kernels (kernels.cu)
 // and returns RTR_CUDA_ERROR when no device is usable.
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -114,6 +115,11 @@ static rtr_status context_init(rtr_context* ctx, int device, void* stream) {
         if (v >= 1024) ctx->wf_target_paths = (uint64_t)v;
     }
     if (const char* e = std::getenv("RTR_WF_GRAPH")) ctx->wf_use_graph = std::atoi(e);
+    if (const char* e = std::getenv("RTR_WF_BIN")) {  // 0 = off, 8 = octant, 24 = octant x dominant axis
+        const int v = std::atoi(e);
+        ctx->wf_bin_keys = v <= 0 ? 0u : v <= 8 ? 8u : 24u;
+    }
+    if (const char* e = std::getenv("RTR_WF_BIN_LAST")) ctx->wf_bin_last_bounce = (uint32_t)std::max(0, std::atoi(e));
     if (const char* e = std::getenv("RTR_SCAN_KERNEL")) ctx->use_scan_kernel = std::atoi(e);
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->wf_counters, WFC_WORDS * sizeof(uint32_t)));
@@ -381,13 +387,20 @@ rtr_status rtr::check_render_args(rtr_context* ctx, const rtr_scene* scene, cons
 // Every queue size lives on the device, so the launch sequence of a wave is fixed: it is captured into a
 // CUDA graph once per call and replayed for each wave (plain launches when capture or instantiation fails).
 static cudaError_t wf_launch_wave(rtr_context* ctx, WfArgs a, const WfPaths buf[2], bool exhaustive, bool count_work,
-                                  int gen_grid, int ext_grid, int shade_grid, int sum_grid, uint32_t* launches) {
+                                  int gen_grid, int ext_grid, int shade_grid, int sum_grid, int bin_grid, uint32_t* launches) {
     cudaError_t e = cudaSuccess;
     auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; ++*launches; };
     a.bounce = 0; a.in = buf[0]; a.out = buf[1];
     step(launch_wf_generate(a, gen_grid, ctx->stream));
+    uint32_t* const perm = a.perm_out;
     for (uint32_t b = 0; b < a.max_ray_depth; ++b) {
         a.bounce = b; a.in = buf[b & 1]; a.out = buf[(b + 1) & 1];
+        a.perm = nullptr;
+        // camera rays arrive in tile order and are coherent as they are; scattered rays are regrouped by direction
+        if (perm && b >= 1 && b <= ctx->wf_bin_last_bounce) {
+            step(launch_wf_bin(a, bin_grid, ctx->stream));
+            a.perm = perm;
+        }
         step(launch_wf_extend(a, ext_grid, exhaustive, count_work, ctx->stream));
         step(launch_wf_shade(a, shade_grid, count_work, ctx->stream));
     }
@@ -426,14 +439,20 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     if (n_paths > 0x7FFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "wavefront: too many paths per wave");
     const uint32_t n_waves = count ? (uint32_t)((count + ws - 1) / ws) : 0;
     const bool use_lbuf = ws > 1;
+    // direction binning (wavefront.cu wf_bin_kernel): BVH walks only, and only when a bounce follows the first
+    const bool use_bin = ctx->wf_bin_keys != 0u && a.enable_bvh_tree != 0u && a.max_ray_depth > 1u && n_paths >= RTR_WF_BIN_BLOCK;
     const size_t streams = 7 + (use_lbuf ? 1 : 0);
-    CU(grow(&ctx->wf_state, &ctx->wf_state_elems, streams * (size_t)n_paths));
+    const size_t perm_elems = use_bin ? ((size_t)n_paths + 3) / 4 : 0;  // n_paths uint32 in float4 units
+    CU(grow(&ctx->wf_state, &ctx->wf_state_elems, streams * (size_t)n_paths + perm_elems));
     WfPaths buf[2];
     float4* s0 = ctx->wf_state;
     buf[0].o = s0; buf[0].d = s0 + n_paths; buf[0].thr = s0 + 2 * n_paths;
     buf[1].o = s0 + 3 * n_paths; buf[1].d = s0 + 4 * n_paths; buf[1].thr = s0 + 5 * n_paths;
     a.hit = s0 + 6 * n_paths;
     a.lbuf = use_lbuf ? s0 + 7 * n_paths : nullptr;
+    a.perm = nullptr;
+    a.perm_out = use_bin ? reinterpret_cast<uint32_t*>(s0 + streams * (size_t)n_paths) : nullptr;
+    a.bin_keys = ctx->wf_bin_keys;
     a.accum = accum_dev;
     a.counters = ctx->wf_counters;
     a.stats = ctx->stats;
@@ -448,6 +467,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     const int gen_grid = blocks_for(n_paths + 32 * (uint64_t)ws * (W / 8 + H / 4 + 2), 16);
     const int shade_grid = blocks_for(n_paths, 16);
     const int sum_grid = blocks_for(n_pixels, 8);
+    const int bin_grid = (int)std::min<uint64_t>((n_paths + RTR_WF_BIN_BLOCK - 1) / RTR_WF_BIN_BLOCK, (uint64_t)ctx->sm_count * 8);
     if (reset_stats) CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
     uint32_t launches = 0;
     if (timed) CU(cudaEventRecord(ctx->ev0, ctx->stream));
@@ -460,7 +480,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
         uint32_t per_wave = 0;
         cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
         if (e == cudaSuccess) {
-            cudaError_t le = wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, &per_wave);
+            cudaError_t le = wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, bin_grid, &per_wave);
             e = cudaStreamEndCapture(ctx->stream, &graph);  // always ends the capture, also after a failed launch
             if (e == cudaSuccess && le != cudaSuccess) e = le;
         }
@@ -483,7 +503,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     }
     if (!done)
         for (uint32_t w = 0; w < n_waves; ++w)
-            CU(wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, &launches));
+            CU(wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, bin_grid, &launches));
     if (timed) CU(cudaEventRecord(ctx->ev1, ctx->stream));
     if (stats_out) {
         std::memset(stats_out, 0, sizeof(*stats_out));

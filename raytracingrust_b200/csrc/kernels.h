@@ -133,6 +133,10 @@ struct WfArgs {
     float4* lbuf;                       // wave_samples * n_pixels clamped sample radiances (wave_samples > 1)
     uint32_t* counters;                 // WFC_WORDS words, see enum
     unsigned long long* stats;
+    // direction binning of bounces >= 1 (wf_bin_kernel): perm[i] = slot of `in` the i-th fetch of wf_extend takes
+    const uint32_t* perm;               // null: slots are fetched in stream order
+    uint32_t* perm_out;                 // what wf_bin writes (the same buffer)
+    uint32_t bin_keys;                  // 8: direction octant; 24: octant x dominant axis
 };
 
 int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes);
@@ -141,6 +145,9 @@ cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st);
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
 cudaError_t launch_wf_shade(const WfArgs& a, int grid, bool count, cudaStream_t st);
 cudaError_t launch_wf_end_wave(const WfArgs& a, int grid, cudaStream_t st);  // ordered sum of lbuf + advance the wave
+// stable counting sort of every RTR_WF_BIN_BLOCK consecutive queued paths by ray-direction key -> perm_out
+#define RTR_WF_BIN_BLOCK 1024
+cudaError_t launch_wf_bin(const WfArgs& a, int grid, cudaStream_t st);
 
 }  // namespace rtr
 #endif
