@@ -33,7 +33,7 @@ struct rtr_context {
     uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
     uint64_t wf_target_paths = 1ull << 24;  // RTR_WF_PATHS: paths in flight per wave (swept 2^22..2^25 on B200; 2.1 GB of path state)
     int wf_use_graph = 1;  // RTR_WF_GRAPH
-    uint32_t wf_bin_keys = 8;  // RTR_WF_BIN: direction-binning keys of bounces >= 1 (0 = off, 8 = octant, 24 = octant x major axis)
+    uint32_t wf_bin_keys = 0;  // RTR_WF_BIN: direction-binning keys of bounces >= 1 (0 = off: measured -1..-7 %; 8 = octant, 24 = octant x major axis)
     uint32_t wf_bin_last_bounce = 255;  // RTR_WF_BIN_LAST: bin bounces 1..this
     int use_scan_kernel = 1;  // RTR_SCAN_KERNEL: 0 sends all-sphere BVH-off renders through the generic megakernel
     char* batch_in = nullptr; size_t batch_in_bytes = 0;

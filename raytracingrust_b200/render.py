@@ -13,7 +13,8 @@ import numpy as np
 from . import _abi as A
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtr_b200.so")
+# RTR_LIBRARY: load another build of the same ABI (same-box A/B of kernel variants, tools/ab.py)
+LIB_PATH = os.environ.get("RTR_LIBRARY") or os.path.join(_HERE, "librtr_b200.so")
 _LIB = None
 
 
