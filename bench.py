@@ -457,6 +457,45 @@ class Bench:
         return rec
 
 
+def measure_trace_batches(b):
+    """BASELINE configs[2] as a batch-API number: rtr_trace_batch on the 1 M-sphere BVH, 2^22 primary rays (pinhole
+    2048x2048 from (0,0,120)) and 2^22 secondary rays (hit point, normal + unit-sphere sample; misses re-drawn as random
+    rays).  `value` = rays / device time of the call's kernels (library events); `e2e` = rays / wall time of the call with
+    host buffers (100 MB of rays H2D + 201 MB of hit records D2H inside).  Every rank traces the same batches."""
+    import _scenes
+    from raytracingrust_b200 import _abi as A
+    scene = _scenes.random_spheres(1_000_000)
+    ds = b.ctx.upload(scene)
+    p = b.rt.make_params(scene, 2048, 2048, seed=0)
+    pix = np.arange(2048 * 2048, dtype=np.uint32)
+    primary = b.ctx.camera_rays(p, pix, np.zeros_like(pix))
+    h = ds.trace_batch(primary)
+    hit = h["object"] != A.RTR_NO_HIT
+    rng = np.random.default_rng(1)
+    u = rng.normal(size=(len(primary), 3)).astype(np.float32)
+    u /= np.linalg.norm(u, axis=1, keepdims=True)
+    secondary = np.zeros(len(primary), A.RAY_DTYPE)
+    secondary["origin"] = np.where(hit[:, None], h["point"], rng.uniform(-50, 50, (len(primary), 3)).astype(np.float32))
+    secondary["direction"] = np.where(hit[:, None], h["normal"] + u, u)
+    out = {"config_id": "C3-batches", "unit": "Mrays/s", "rays_per_batch": len(primary),
+           "workload": "rtr_trace_batch, 1M random spheres (seed 42): 2^22 primary + 2^22 secondary rays, closest-hit records out",
+           "kernel": "trace_unpack + wf_extend + trace_finish (the render's persistent majority-rule walk)"}
+    for name, rays in (("primary", primary), ("secondary", secondary)):
+        dev_ms, wall = [], []
+        for i in range(4):
+            t0 = time.perf_counter()
+            hits, st = ds.trace_batch(rays, want_stats=True)
+            wall.append(time.perf_counter() - t0)
+            dev_ms.append(st["device_ms"])
+        _, sc = ds.trace_batch(rays, want_stats=True, flags=A.FLAG_COUNT_WORK)
+        out[name] = {"value": len(rays) / (float(np.mean(dev_ms[1:])) * 1e-3) / 1e6, "device_ms": float(np.mean(dev_ms[1:])),
+                     "e2e": len(rays) / min(wall[1:]) / 1e6, "h2d_bytes": int(rays.nbytes), "d2h_bytes": int(hits.nbytes),
+                     "nodes_per_ray": sc["nodes_visited"] / len(rays), "sphere_tests_per_ray": sc["sphere_tests"] / len(rays),
+                     "hit_fraction": float((hits["object"] != A.RTR_NO_HIT).mean())}
+    ds.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -484,6 +523,10 @@ def main():
             rec = b.measure(name, steps, 3, spp_cap=cap, e2e_spp=e2e_spp, warmup_spp=max(1, min(16, (1 << 26) // (WORKLOADS[name]["W"] * WORKLOADS[name]["H"]))))
             if rec is not None:
                 subs[name] = rec
+    if not args.no_workloads and args.workload == "benchmark":
+        tb = measure_trace_batches(b)
+        if b.rank == 0:
+            subs["trace_batches"] = tb
     if b.rank == 0:
         out["warmup"] = args.warmup
         if subs:

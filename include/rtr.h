@@ -267,7 +267,9 @@ rtr_status rtr_group_device_stats(const rtr_group* group, uint32_t index, rtr_st
 rtr_status rtr_group_set_split(rtr_group* group, uint32_t split, uint32_t chunk);
 
 /* world.hit(ray, tmin, +INF) for explicit rays (render.rs:38).  Ray i draws any
- * volume random numbers from counter (pixel=i, sample=0, bounce=0). */
+ * volume random numbers from counter (pixel=i, sample=0, bounce=0).  Runs the render's own traversal kernel
+ * (wf_extend) on the batch.  stats_out (may be NULL): rays, device_ms of the kernels (copies excluded); the work
+ * counters are filled only under RTR_FLAG_COUNT_WORK or RTR_FLAG_REFERENCE_TREE. */
 rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays,
                            size_t n, float tmin, uint32_t enable_bvh_tree, uint32_t flags,
                            uint64_t seed, rtr_hit* hits_out, rtr_stats* stats_out);

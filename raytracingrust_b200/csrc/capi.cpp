@@ -428,6 +428,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
     a.sample_begin = p->sample_begin; a.sample_end = p->sample_begin + count;
     a.refill_threshold = ctx->wf_refill_threshold;
+    a.tmin = 0.00001f;  // render.rs:38
     a.accumulate = (p->flags & RTR_FLAG_ACCUMULATE) ? 1u : 0u;
     // samples of every pixel in flight per wave: enough paths to fill the chip, bounded scratch
     uint64_t ws = n_pixels ? ctx->wf_target_paths / n_pixels : 1;
@@ -666,19 +667,48 @@ rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_r
     if (n == 0) return RTR_OK;
     if (n > 0xFFFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "batch too large (ray index is the u32 RNG counter)");
     CU(cudaSetDevice(ctx->device));
+    // The walk is the render's own: wf_extend (persistent warps, majority-rule stepping, lane refill, shared-memory
+    // short stack), fed from the queue of bounce 0.  Work counters only under RTR_FLAG_COUNT_WORK / RTR_FLAG_REFERENCE_TREE;
+    // stats_out->device_ms always times the three kernels (events on the context stream, copies outside).
+    const bool exhaustive = (flags & RTR_FLAG_EXHAUSTIVE) != 0;
+    const bool count_work = (flags & (RTR_FLAG_COUNT_WORK | RTR_FLAG_REFERENCE_TREE)) != 0;  // the reference-topology walk lives in the counting instantiations
+    const size_t piece = std::min<size_t>(n, (size_t)1 << 24);  // rays per pass: bounds the scratch (48 B per ray)
     CU(grow(&ctx->batch_in, &ctx->batch_in_bytes, n * sizeof(rtr_ray)));
     CU(grow(&ctx->batch_out, &ctx->batch_out_bytes, n * sizeof(rtr_hit)));
+    CU(grow(&ctx->wf_state, &ctx->wf_state_elems, 3 * piece));
+    WfArgs a;
+    std::memset(&a, 0, sizeof(a));
+    a.sc = view_for(scene, flags);
+    a.max_ray_depth = 1;
+    a.enable_bvh_tree = enable_bvh_tree;
+    a.k0 = (uint32_t)seed; a.k1 = (uint32_t)(seed >> 32);
+    a.sample_begin = 0; a.sample_end = 1; a.wave_samples = 1;
+    a.refill_threshold = ctx->wf_refill_threshold;
+    a.tmin = tmin;
+    a.in.o = ctx->wf_state; a.in.d = ctx->wf_state + piece; a.hit = ctx->wf_state + 2 * piece;
+    a.counters = ctx->wf_counters;
+    a.stats = ctx->stats;
+    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || enable_bvh_tree == 0u, tmin != 0.00001f);
+    if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
     CU(cudaMemcpyAsync(ctx->batch_in, rays, n * sizeof(rtr_ray), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(launch_trace_batch(view_for(scene, flags), (const rtr_ray*)ctx->batch_in, n, tmin, enable_bvh_tree,
-                          (flags & RTR_FLAG_EXHAUSTIVE) != 0, (uint32_t)seed, (uint32_t)(seed >> 32),
-                          (rtr_hit*)ctx->batch_out, ctx->stats, ctx->stream));
+    uint32_t launches = 0;
+    for (size_t first = 0; first < n; first += piece) {
+        const uint32_t m = (uint32_t)std::min(piece, n - first);
+        CU(cudaMemsetAsync(ctx->wf_counters, 0, WFC_WORDS * sizeof(uint32_t), ctx->stream));
+        CU(launch_trace_unpack(a, (const rtr_ray*)ctx->batch_in + first, m, (uint32_t)first, ctx->stream));
+        uint64_t blocks = ((uint64_t)m + RTR_WF_EXTEND_THREADS - 1) / RTR_WF_EXTEND_THREADS;
+        const uint64_t cap = (uint64_t)ctx->sm_count * per_sm;
+        CU(launch_wf_extend(a, (int)(blocks < 1 ? 1 : blocks > cap ? cap : blocks), exhaustive, count_work, ctx->stream));
+        CU(launch_trace_finish(a, m, (rtr_hit*)ctx->batch_out + first, ctx->stream));
+        launches += 3;
+    }
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     CU(cudaMemcpyAsync(hits_out, ctx->batch_out, n * sizeof(rtr_hit), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     if (stats_out) {
-        stats_out->rays = n; stats_out->kernel_launches = 1; stats_out->kernel_used = RTR_KERNEL_MEGAKERNEL;
+        stats_out->kernel_launches = launches; stats_out->kernel_used = RTR_KERNEL_WAVEFRONT;
         rtr_status st = collect_stats(ctx, true, stats_out);
         stats_out->rays = n;
         return st;

@@ -242,45 +242,7 @@ cudaError_t launch_expand_env(const float* rgb, float4* out, size_t n, cudaStrea
 }
 
 // ------------------------------------------------------------------ batch (parity) kernels
-template <bool EXHAUSTIVE>
-__global__ void __launch_bounds__(128) trace_batch_kernel(const SceneView sc, const rtr_ray* rays, size_t n, float tmin,
-                                                          uint32_t bvh, uint32_t k0, uint32_t k1, rtr_hit* out,
-                                                          unsigned long long* stats) {
-    StackEntry stack[RTR_STACK_CAP];
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    Ray r;
-    r.o = mk(rays[i].origin.x, rays[i].origin.y, rays[i].origin.z);
-    r.d = mk(rays[i].direction.x, rays[i].direction.y, rays[i].direction.z);
-    RngKey key; key.k0 = k0; key.k1 = k1; key.pixel = (uint32_t)i; key.sample = 0; key.bounce = 0;
-    Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
-    const LiteHit lh = world_hit<EXHAUSTIVE, true>(sc, bvh != 0, r, tmin, key, stack, &cnt);
-    rtr_hit h;
-#ifdef RTR_DEBUG_BOUNDS
-    if (lh.t == -12345.0f || lh.t == -54321.0f) {
-        h.object = 0xDEADBEEFu; h.primitive = lh.ref; h.t = lh.t; h.point.x = lh.u; h.point.y = h.point.z = 0.0f;
-        h.normal.x = h.normal.y = h.normal.z = 0.0f; h.front_face = 0; h.material = 0;
-        out[i] = h;
-        return;
-    }
-#endif
-    if (lh.ref == REF_EMPTY_VALUE) {
-        h.object = RTR_NO_HIT; h.primitive = 0; h.t = 0.0f;
-        h.point.x = h.point.y = h.point.z = 0.0f; h.normal.x = h.normal.y = h.normal.z = 0.0f;
-        h.front_face = 0; h.material = 0;
-    } else {
-        const Hit f = finish_hit(sc, r, lh);
-        h.object = f.object; h.primitive = f.primitive; h.t = f.t;
-        h.point.x = f.point.x; h.point.y = f.point.y; h.point.z = f.point.z;
-        h.normal.x = f.normal.x; h.normal.y = f.normal.y; h.normal.z = f.normal.z;
-        h.front_face = f.front_face ? 1u : 0u; h.material = f.material;
-    }
-    out[i] = h;
-    atomicAdd(&stats[STAT_NODES], (unsigned long long)cnt.nodes);
-    atomicAdd(&stats[STAT_TRIS], (unsigned long long)cnt.tris);
-    atomicAdd(&stats[STAT_SPHERES], (unsigned long long)cnt.spheres);
-}
-
+// (rtr_trace_batch runs on the wavefront's wf_extend: trace_unpack / trace_finish in wavefront.cu)
 __global__ void scatter_batch_kernel(const SceneView sc, const rtr_scatter_in* in, size_t n, uint32_t mode,
                                      uint32_t k0, uint32_t k1, rtr_scatter_out* out) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -358,15 +320,6 @@ cudaError_t launch_sum_chunks(const float4* partials, float4* accum, uint32_t n_
 
 cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels, float spp, cudaStream_t st) {
     resolve_kernel<<<(n_pixels + 255) / 256, 256, 0, st>>>(accum, rgba, n_pixels, spp);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_trace_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float tmin, uint32_t bvh,
-                               bool exhaustive, uint32_t k0, uint32_t k1, rtr_hit* out, unsigned long long* stats,
-                               cudaStream_t st) {
-    const unsigned grid = (unsigned)((n + 127) / 128);
-    if (exhaustive) trace_batch_kernel<true><<<grid, 128, 0, st>>>(sc, rays, n, tmin, bvh, k0, k1, out, stats);
-    else trace_batch_kernel<false><<<grid, 128, 0, st>>>(sc, rays, n, tmin, bvh, k0, k1, out, stats);
     return cudaGetLastError();
 }
 

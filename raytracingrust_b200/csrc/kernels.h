@@ -79,9 +79,6 @@ cudaError_t launch_resolve(const float4* accum, uchar4* rgba, uint32_t n_pixels,
 struct PeerAccum { const float4* accum[RTR_MAX_GROUP]; };
 cudaError_t launch_reduce_resolve_peers(const PeerAccum& peers, uint32_t n_ranks, float4* accum_root, uchar4* rgba_root,
                                         uint32_t lo, uint32_t hi, float spp, cudaStream_t st);
-cudaError_t launch_trace_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float tmin, uint32_t bvh,
-                               bool exhaustive, uint32_t k0, uint32_t k1, rtr_hit* out, unsigned long long* stats,
-                               cudaStream_t st);
 cudaError_t launch_scatter_batch(const SceneView& sc, const rtr_scatter_in* in, size_t n, uint32_t mode, uint32_t k0,
                                  uint32_t k1, rtr_scatter_out* out, cudaStream_t st);
 cudaError_t launch_background_batch(const SceneView& sc, const rtr_ray* rays, size_t n, float* rgb, cudaStream_t st);
@@ -126,6 +123,7 @@ struct WfArgs {
     uint32_t wave_samples;              // samples of every pixel in flight per wave
     uint32_t bounce;                    // which [extend, shade] pair this launch is
     uint32_t refill_threshold;          // extend refills idle lanes when fewer lanes than this are walking
+    float tmin;                         // world.hit(ray, tmin, +INF): 0.00001 in render() (render.rs:38); the caller's in rtr_trace_batch
     uint32_t accumulate;                // RTR_FLAG_ACCUMULATE: keep what accum already holds
     WfPaths in, out;
     float4* hit;                        // per slot of `in`: (t, bits(ref), u, v)
@@ -139,12 +137,16 @@ struct WfArgs {
     uint32_t bin_keys;                  // 8: direction octant; 24: octant x dominant axis
 };
 
-int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes);
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg = false);
 cudaError_t launch_wf_begin(const WfArgs& a, cudaStream_t st);       // zero accum + wave counter
 cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st);
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
 cudaError_t launch_wf_shade(const WfArgs& a, int grid, bool count, cudaStream_t st);
 cudaError_t launch_wf_end_wave(const WfArgs& a, int grid, cudaStream_t st);  // ordered sum of lbuf + advance the wave
+// rtr_trace_batch = unpack (AoS rays -> the wavefront's ray streams, queue size n) -> wf_extend (the render's own
+// persistent, majority-rule, short-stack walk) -> finish (HitRecord of every winner -> AoS rtr_hit)
+cudaError_t launch_trace_unpack(const WfArgs& a, const rtr_ray* rays, uint32_t n, uint32_t first_index, cudaStream_t st);
+cudaError_t launch_trace_finish(const WfArgs& a, uint32_t n, rtr_hit* out, cudaStream_t st);
 // stable counting sort of every RTR_WF_BIN_BLOCK consecutive queued paths by ray-direction key -> perm_out
 #define RTR_WF_BIN_BLOCK 1024
 cudaError_t launch_wf_bin(const WfArgs& a, int grid, cudaStream_t st);

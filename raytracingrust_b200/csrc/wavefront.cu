@@ -175,8 +175,11 @@ __global__ void __launch_bounds__(256) wf_bin_kernel(const WfArgs a) {
 // VOLUMES = false: the scene holds no Volume and the BVH is on (every shipped scene but C5).  Volume::hit is a
 // non-inlined call with two nested walks; compiling it out of the walk removes the call's register save/restore
 // and the per-ray RNG key from the traversal state (ncu: local-memory traffic was 44 % of wf_extend's L1 wavefronts).
-template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES>
+// TMIN_ARG = true: world.hit's tmin comes from the arguments (rtr_trace_batch with a tmin other than render()'s 1e-5);
+// the render path keeps the literal, which costs the volume instantiation 30 bytes of spills less.
+template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES, bool TMIN_ARG = false>
 __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL) wf_extend_kernel(const WfArgs a) {
+    const float tmin0 = TMIN_ARG ? a.tmin : 0.00001f;  // render.rs:38
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
     __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_EXTEND_THREADS];
     ShortStack<RTR_SHORT_STACK, RTR_WF_EXTEND_THREADS> wstack;
@@ -195,7 +198,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
             Ray r; r.o = xyz(o); r.d = xyz(d);
             RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = __float_as_uint(o.w);
             key.sample = w.begin + (__float_as_uint(d.w) >> 8); key.bounce = __float_as_uint(d.w) & 0xFFu;
-            const LiteHit h = world_hit<EXHAUSTIVE, COUNT>(a.sc, false, r, 0.00001f, key, stack, &cnt);
+            const LiteHit h = world_hit<EXHAUSTIVE, COUNT>(a.sc, false, r, tmin0, key, stack, &cnt);
             a.hit[i] = make_float4(h.t, __uint_as_float(h.ref), h.u, h.v);
         }
     } else {
@@ -214,7 +217,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
         // phase 2 ends the medium is sampled (volume_sample), the outer walk is restored and offered the hit.
         uint32_t vstate = 0u;       // 0: outer walk; else phase (1 | 2) << 30 | index in volumes[]
         int floor = 0;              // the nested walk's stack bottom
-        float tmin_cur = 0.00001f;  // tmin of the walk in progress (render.rs:38; volume.rs:36-37)
+        float tmin_cur = tmin0;  // tmin of the walk in progress (render.rs:38; volume.rs:36-37)
         for (;;) {
             // ---- refill idle lanes from the stream: one atomic per warp  [bucket:wf_fetch]
             const uint32_t idle = __ballot_sync(FULL, !has);
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                         best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
                         cur = walk_entry(a.sc.root_entry);
                         sp = 0;
-                        if (VOLUMES) { vstate = 0u; floor = 0; tmin_cur = 0.00001f; }
+                        if (VOLUMES) { vstate = 0u; floor = 0; tmin_cur = tmin0; }
                         has = true;
                     }
                 }
@@ -254,9 +257,9 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
                     if (at_node) {
-                        node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : 0.00001f, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
+                        node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
 #if RTR_WF_NODE_BURST
-                        if (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : 0.00001f, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
+                        if (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
 #endif
                     }
                 }
@@ -278,7 +281,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                         }
                     } else {
                         // nested walks never meet a Volume leaf (flat.h: a boundary is a sphere or a mesh)
-                        leaf_step<EXHAUSTIVE, COUNT, false, false>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : 0.00001f, key, wstack, &cnt, VOLUMES ? floor : 0);
+                        leaf_step<EXHAUSTIVE, COUNT, false, false>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, key, wstack, &cnt, VOLUMES ? floor : 0);
                     }
                 }
                 if (VOLUMES && vstate != 0u && cur == RTR_REF_DONE) {  // a boundary query has finished  [bucket:volume_fsm]
@@ -290,7 +293,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                         wstack.put(sp, 0u, t1); ++sp;
                         floor = sp;
                         vstate = (2u << 30) | vidx;
-                        tmin_cur = t1 + 0.00001f;
+                        tmin_cur = t1 + tmin0;
                         best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
                         cur = walk_entry(a.sc.reference_tree ? vol.entry_reference : vol.entry);
                     } else {
@@ -299,13 +302,13 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                         if (second) {
                             base = floor - 1;
                             if (best.ref != REF_EMPTY_VALUE)
-                                t_hit = volume_sample(vol, r, wstack.get(floor - 1).enter, best.t, 0.00001f, RTR_INF, key);
+                                t_hit = volume_sample(vol, r, wstack.get(floor - 1).enter, best.t, tmin0, RTR_INF, key);
                         }
                         const StackEntry uv = wstack.get(base - 1), tr = wstack.get(base - 2);
                         sp = base - 2;
                         best.t = tr.enter; best.ref = tr.ref; best.u = __uint_as_float(uv.ref); best.v = uv.enter;
                         if (t_hit == t_hit) offer(a.sc, best, t_hit, RTR_MAKE_REF(REF_VOLUME, vidx), 0.0f, 0.0f);
-                        vstate = 0u; floor = 0; tmin_cur = 0.00001f;
+                        vstate = 0u; floor = 0; tmin_cur = tmin0;
                         cur = pop_next<EXHAUSTIVE>(wstack, sp, best.t, 0);
                     }
                 }
@@ -428,10 +431,54 @@ __global__ void wf_next_wave_kernel(const WfArgs a) {
     if (threadIdx.x == 0) a.counters[WFC_WAVE] += 1u;
 }
 
+// ------------------------------------------------------------------ rtr_trace_batch on the wavefront walk
+// world.hit(ray, tmin, +INF) for caller-supplied rays (include/rtr.h): the rays are unpacked into the queue of bounce 0,
+// wf_extend walks them exactly as it walks a render's rays, and the winners' HitRecords are rebuilt for the caller.
+// Ray i draws its volume random numbers from counter (pixel = i, sample 0, bounce 0).
+__global__ void trace_unpack_kernel(const WfArgs a, const rtr_ray* rays, uint32_t n, uint32_t first_index) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) a.counters[WFC_QCOUNT] = n;
+    if (i >= n) return;
+    const rtr_ray r = rays[i];
+    a.in.o[i] = make_float4(r.origin.x, r.origin.y, r.origin.z, __uint_as_float(first_index + i));
+    a.in.d[i] = make_float4(r.direction.x, r.direction.y, r.direction.z, __uint_as_float(0u));
+}
+
+__global__ void trace_finish_kernel(const WfArgs a, uint32_t n, rtr_hit* out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 o = a.in.o[i], d = a.in.d[i], hq = a.hit[i];
+    Ray r; r.o = xyz(o); r.d = xyz(d);
+    LiteHit lh; lh.t = hq.x; lh.ref = __float_as_uint(hq.y); lh.u = hq.z; lh.v = hq.w;
+    rtr_hit h;
+    if (lh.ref == REF_EMPTY_VALUE) {
+        h.object = RTR_NO_HIT; h.primitive = 0; h.t = 0.0f;
+        h.point.x = h.point.y = h.point.z = 0.0f; h.normal.x = h.normal.y = h.normal.z = 0.0f;
+        h.front_face = 0; h.material = 0;
+    } else {
+        const Hit f = finish_hit(a.sc, r, lh);
+        h.object = f.object; h.primitive = f.primitive; h.t = f.t;
+        h.point.x = f.point.x; h.point.y = f.point.y; h.point.z = f.point.z;
+        h.normal.x = f.normal.x; h.normal.y = f.normal.y; h.normal.z = f.normal.z;
+        h.front_face = f.front_face ? 1u : 0u; h.material = f.material;
+    }
+    out[i] = h;
+}
+
+cudaError_t launch_trace_unpack(const WfArgs& a, const rtr_ray* rays, uint32_t n, uint32_t first_index, cudaStream_t st) {
+    trace_unpack_kernel<<<(n + 255u) / 256u, 256, 0, st>>>(a, rays, n, first_index);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace_finish(const WfArgs& a, uint32_t n, rtr_hit* out, cudaStream_t st) {
+    trace_finish_kernel<<<(n + 127u) / 128u, 128, 0, st>>>(a, n, out);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------ launchers
 template <typename F>
-static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, F f) {
-#define RTR_PICK(E, C, V) return f(wf_extend_kernel<E, C, V>)
+static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_arg, F f) {
+#define RTR_PICK(E, C, V) do { if (tmin_arg) return f(wf_extend_kernel<E, C, V, true>); return f(wf_extend_kernel<E, C, V, false>); } while (0)
     if (exhaustive) {
         if (count) { if (volumes) RTR_PICK(true, true, true); else RTR_PICK(true, true, false); }
         else { if (volumes) RTR_PICK(true, false, true); else RTR_PICK(true, false, false); }
@@ -442,9 +489,9 @@ static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, F f) {
 #undef RTR_PICK
 }
 
-int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes) {
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg) {
     int n = 0;
-    cudaError_t e = pick_wf_extend(exhaustive, count, volumes, [&](void (*k)(const WfArgs)) {
+    cudaError_t e = pick_wf_extend(exhaustive, count, volumes, tmin_arg, [&](void (*k)(const WfArgs)) {
         return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_WF_EXTEND_THREADS, 0);
     });
     return e == cudaSuccess ? n : 0;
@@ -464,7 +511,8 @@ cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st) {
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st) {
     // the generic instantiation also carries the BVH-off linear scan
     const bool volumes = a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u;
-    pick_wf_extend(exhaustive, count, volumes, [&](void (*k)(const WfArgs)) {
+    const bool tmin_arg = a.tmin != 0.00001f;
+    pick_wf_extend(exhaustive, count, volumes, tmin_arg, [&](void (*k)(const WfArgs)) {
         k<<<grid, RTR_WF_EXTEND_THREADS, 0, st>>>(a);
         return cudaSuccess;
     });
