@@ -273,6 +273,22 @@ rtr_status rtr_group_set_split(rtr_group* group, uint32_t split, uint32_t chunk)
 rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays,
                            size_t n, float tmin, uint32_t enable_bvh_tree, uint32_t flags,
                            uint64_t seed, rtr_hit* hits_out, rtr_stats* stats_out);
+/* rtr_trace_batch for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code that must not call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same result as rtr_trace_batch, but rays_dev and hits_dev are DEVICE buffers of the context's device supplied
+ * by the caller, and the kernels' scratch (ray / hit streams, queue counters) is a static device array inside the
+ * library: RTR_NOALLOC_SCRATCH_BYTES of device memory held by every GPU that loads the library until the process
+ * exits.  The call allocates nothing (no cudaMalloc / cudaFree / pool allocation), copies nothing to or from the host
+ * and does not synchronise: it enqueues one memset + three kernels on the context's stream; call rtr_synchronize (or
+ * order your own stream after it) before reading hits_dev.  n > RTR_NOALLOC_MAX_RAYS -> RTR_INVALID_ARG.
+ * flags: RTR_FLAG_EXHAUSTIVE and RTR_FLAG_REFERENCE_TREE only.  All calls on one device share the one scratch array:
+ * calls that overlap on the GPU (two streams or two contexts of a device) race on it — serialise them.  The first
+ * call on a device looks the array's address up (cudaGetSymbolAddress); make it before starting a graph capture. */
+#define RTR_NOALLOC_MAX_RAYS 262144u
+#define RTR_NOALLOC_SCRATCH_BYTES 12587008u /* 4096 + 3 streams x 16 B x RTR_NOALLOC_MAX_RAYS */
+rtr_status rtr_trace_batch_device_noalloc(rtr_context* ctx, const rtr_scene* scene, const rtr_ray* rays_dev,
+                                          size_t n, float tmin, uint32_t enable_bvh_tree, uint32_t flags,
+                                          uint64_t seed, rtr_hit* hits_dev);
 /* Material::scatter (materials.rs, volume.rs:82-87); mode FULL or CLAY (render.rs:40-41) */
 rtr_status rtr_scatter_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_scatter_in* in,
                              size_t n, uint32_t mode, uint64_t seed, rtr_scatter_out* out);

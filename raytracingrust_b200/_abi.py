@@ -23,6 +23,7 @@ FLAG_REFERENCE_TREE = 4
 FLAG_ACCUMULATE = 8
 REDUCE_AUTO, REDUCE_NCCL, REDUCE_P2P = range(3)
 SPLIT_STATIC, SPLIT_DYNAMIC = range(2)
+NOALLOC_MAX_RAYS = 262144
 
 f32, u32, u64, f64 = C.c_float, C.c_uint32, C.c_uint64, C.c_double
 
@@ -140,7 +141,7 @@ EXPORTED_SYMBOLS = [
     "rtr_abi_version", "rtr_context_create", "rtr_context_destroy", "rtr_last_error",
     "rtr_scene_upload", "rtr_scene_destroy", "rtr_scene_info", "rtr_render",
     "rtr_render_accumulate_device", "rtr_resolve_device", "rtr_synchronize",
-    "rtr_trace_batch", "rtr_scatter_batch", "rtr_background_batch", "rtr_camera_rays",
+    "rtr_trace_batch", "rtr_trace_batch_device_noalloc", "rtr_scatter_batch", "rtr_background_batch", "rtr_camera_rays",
     "rtr_group_create", "rtr_group_destroy", "rtr_group_size", "rtr_group_reduce_mode", "rtr_group_last_error",
     "rtr_group_scene_upload", "rtr_group_scene_destroy", "rtr_group_render", "rtr_group_device_stats",
     "rtr_group_set_split",

@@ -49,6 +49,7 @@ def lib():
     L.rtr_resolve_device.argtypes = [vp, vp, u32, u32, u32, vp]
     L.rtr_synchronize.argtypes = [vp]
     L.rtr_trace_batch.argtypes = [vp, vp, vp, sz, C.c_float, u32, u32, u64, vp, C.POINTER(A.Stats)]
+    L.rtr_trace_batch_device_noalloc.argtypes = [vp, vp, vp, sz, C.c_float, u32, u32, u64, vp]
     L.rtr_scatter_batch.argtypes = [vp, vp, vp, sz, u32, u64, vp]
     L.rtr_background_batch.argtypes = [vp, vp, vp, sz, vp]
     L.rtr_camera_rays.argtypes = [vp, C.POINTER(A.RenderParams), vp, vp, sz, vp]
