@@ -926,6 +926,17 @@ static void fill_hit(const HitRecord& h, rtr_hit* o) {
     o->front_face = h.front_face ? 1u : 0u; o->material = h.material;
 }
 
+// AABB::hit (aabb.rs:81-137) on its own, for the second-opinion vectors (tests/golden/vectors): boxes = n x (min.xyz, max.xyz)
+int orc_aabb_hit_batch(const float* boxes, const rtr_ray* rays, size_t n, float tmin, float tmax, uint8_t* out) {
+    for (size_t i = 0; i < n; ++i) {
+        const float* b = boxes + 6 * i;
+        AABB box{V(b[0], b[1], b[2]), V(b[3], b[4], b[5])};
+        Ray ray{V(rays[i].origin.x, rays[i].origin.y, rays[i].origin.z), V(rays[i].direction.x, rays[i].direction.y, rays[i].direction.z)};
+        out[i] = aabb_hit(box, ray, tmin, tmax) ? 1 : 0;
+    }
+    return RTR_OK;
+}
+
 // world.hit(ray, tmin, +INF) for a ray batch (render.rs:38)
 int orc_trace_batch(const orc_scene* s, const rtr_ray* rays, size_t n, float tmin, uint32_t enable_bvh_tree,
                     uint64_t seed, rtr_hit* hits_out) {

@@ -38,6 +38,7 @@ def lib():
         L.orc_render.argtypes = [C.c_void_p, C.POINTER(A.RenderParams), C.c_int, C.c_int, C.c_void_p, C.c_void_p,
                                  C.POINTER(A.Stats)]
         L.orc_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.orc_aabb_hit_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_float, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -112,6 +113,15 @@ class OracleScene:
                                 rgba.ctypes.data if want_rgba else None,
                                 acc.ctypes.data if want_accum else None, C.byref(st)), "render")
         return rgba, acc, st.as_dict()
+
+
+def aabb_hit_batch(boxes, rays, tmin, tmax):
+    """AABB::hit (aabb.rs:81-137) for n (box, ray) pairs; boxes (n, 6) = min.xyz, max.xyz."""
+    boxes = np.ascontiguousarray(boxes, np.float32)
+    rays = np.ascontiguousarray(rays, A.RAY_DTYPE)
+    out = np.zeros(len(rays), np.uint8)
+    _check(lib().orc_aabb_hit_batch(boxes.ctypes.data, rays.ctypes.data, len(rays), tmin, tmax, out.ctypes.data), "aabb_hit_batch")
+    return out.astype(bool)
 
 
 def camera_rays(params, pixels, samples):

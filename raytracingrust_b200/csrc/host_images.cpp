@@ -65,7 +65,7 @@ float half_to_float(uint16_t h) {
 struct Cursor {
     const uint8_t* p;
     const uint8_t* end;
-    void need(size_t n) const { if ((size_t)(end - p) < n) fail("unexpected end of file"); }
+    void need(size_t n) const { if (p > end || (size_t)(end - p) < n) fail("unexpected end of file"); }
     uint8_t u8() { need(1); return *p++; }
     uint32_t u32() { need(4); uint32_t v = p[0] | (p[1] << 8) | (p[2] << 16) | ((uint32_t)p[3] << 24); p += 4; return v; }
     int32_t i32() { return (int32_t)u32(); }
@@ -419,7 +419,7 @@ void load_exr(const std::vector<uint8_t>& file, rtr_host_image& img) {
     img.rgb.assign((size_t)width * height * 3, 0.0f);
     std::vector<uint8_t> tmp, raw;
     for (size_t b = 0; b < n_blocks; ++b) {
-        if (offsets[b] + 8 > file.size()) fail("bad chunk offset");
+        if (offsets[b] > file.size() || file.size() - offsets[b] < 8) fail("bad chunk offset");  // no u64 wrap-around
         Cursor k{file.data() + offsets[b], file.data() + file.size()};
         const int64_t y0 = (int64_t)k.i32() - ymin;
         const int32_t size = k.i32();

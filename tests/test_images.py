@@ -136,3 +136,19 @@ def test_unsupported_and_corrupt_files(tmp_path):
         p.write_bytes(data[:cut])
         with pytest.raises(rt.RtrError):
             rt.load_image(str(p))
+
+
+def test_exr_chunk_offset_near_2_64_is_rejected(tmp_path):
+    """A crafted chunk offset close to 2^64 used to wrap the `offset + 8 > size` check and read out of bounds."""
+    import struct
+    good = tmp_path / "good.exr"
+    rt.write_exr(str(good), _picture(20, 20, 1))  # ZIP, 16 lines per block: two chunks, a two-entry offset table
+    data = bytearray(good.read_bytes())
+    table = next(i for i in range(8, len(data) - 16) if struct.unpack_from("<Q", data, i)[0] == i + 16)
+    for evil in (0xFFFFFFFFFFFFFFFC, 0xFFFFFFFFFFFFFFF8, len(data) - 4, 1 << 63):
+        bad = bytearray(data)
+        struct.pack_into("<Q", bad, table, evil)
+        p = tmp_path / "evil.exr"
+        p.write_bytes(bytes(bad))
+        with pytest.raises(rt.RtrError):
+            rt.load_image(str(p))
