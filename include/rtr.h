@@ -81,8 +81,10 @@ typedef struct rtr_mesh {
     uint32_t _pad;
 } rtr_mesh;
 
-/* Volume (lib/volume.rs:19-23): boundary must be a SPHERE or MESH ref; the boundary
- * object is owned by the volume (it need not appear in `objects`).  neg_inv_density is the
+/* Volume (lib/volume.rs:19-23): boundary is a SPHERE, MESH or VOLUME ref (Box<dyn Object>; a chain of volumes must
+ * end in geometry, a cyclic chain is RTR_INVALID_ARG); the boundary object is owned by the volume (it need not appear
+ * in `objects`).  A volume bounded by a volume never hits in the reference (its inner query runs with tmin = -inf,
+ * volume.rs:36-49) but still takes part in the BVH through its bounds; that is reproduced.  neg_inv_density is the
  * struct's stored field, i.e. -1.0/density as Volume::new computes it (volume.rs:26-31). */
 typedef struct rtr_volume { rtr_object_ref boundary; float neg_inv_density; } rtr_volume;
 

@@ -226,8 +226,7 @@ struct Volume : core::traits::Object {  // lib/volume.rs:19-31: stores -1/densit
     Volume(std::unique_ptr<core::traits::Object> b, utils::Float density) : boundary(std::move(b)), neg_inv_density(-1.0f / density) {}
     bool is_volume() const override { return true; }
     rtr_object_ref lower(core::SceneBuilder& b) const override {
-        if (boundary->is_volume()) throw Panic(RTR_UNSUPPORTED, "Volume bounded by a Volume is unsupported");
-        const rtr_object_ref inner = boundary->lower(b);
+        const rtr_object_ref inner = boundary->lower(b);  // Box<dyn Object>: a Sphere, a Mesh or again a Volume (volume.rs:20-23)
         b.volumes.push_back(rtr_volume{inner, neg_inv_density});
         return rtr_object_ref{RTR_OBJ_VOLUME, (uint32_t)b.volumes.size() - 1u};
     }

@@ -853,8 +853,17 @@ static std::unique_ptr<Object> make_object(const rtr_scene_desc* d, rtr_object_r
         if (ref.index >= d->n_volumes) { *err = "volume index out of range"; return nullptr; }
         const rtr_volume& v = d->volumes[ref.index];
         std::unique_ptr<Volume> vo(new Volume());
-        vo->boundary = make_object(d, v.boundary, volume_counter, false, err, nan_centroid);
-        if (!vo->boundary) { if (err->empty()) *err = "volume boundary must be a sphere or mesh"; return nullptr; }
+        // boundary: Box<dyn Object> (volume.rs:20-23) — a Sphere, a Mesh or again a Volume.  The plain-C description is
+        // index based, so unlike Rust's ownership tree it could loop: follow the chain first.
+        {
+            rtr_object_ref b = v.boundary;
+            for (uint32_t steps = 0; b.kind == RTR_OBJ_VOLUME; ++steps) {
+                if (b.index >= d->n_volumes || steps > d->n_volumes) { *err = "volume boundary chain is cyclic or out of range"; return nullptr; }
+                b = d->volumes[b.index].boundary;
+            }
+        }
+        vo->boundary = make_object(d, v.boundary, volume_counter, true, err, nan_centroid);
+        if (!vo->boundary) { if (err->empty()) *err = "bad volume boundary"; return nullptr; }
         vo->neg_inv_density = v.neg_inv_density;  // as stored by Volume::new (volume.rs:26-31)
         vo->volume_index = ref.index;
         return vo;

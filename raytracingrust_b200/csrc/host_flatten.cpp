@@ -357,14 +357,24 @@ struct Flattener {
         VolumeRec rec;
         std::memset(&rec, 0, sizeof(rec));
         rec.rank = rank++;
-        uint32_t bdepth = 0;
-        Built b = emit_object(v.boundary, object);
-        rec.entry_reference = make_entry(b, &bdepth);
-        rec.entry = traversal_entry(b);
-        out.max_boundary_depth = std::max(out.max_boundary_depth, std::max(bdepth, b.fast_depth + 1));
+        rtr_object_ref geom = v.boundary;  // the geometry at the end of the boundary chain: bounds() and material() forward to it
+        while (geom.kind == RTR_OBJ_VOLUME) geom = d.volumes[geom.index].boundary;  // validated: terminates
+        if (v.boundary.kind == RTR_OBJ_VOLUME) {
+            // A Volume bounded by a Volume never hits.  Its first query is boundary.hit(ray, -inf, +inf) (volume.rs:36),
+            // i.e. the inner Volume::hit with tmin = -inf: there the second boundary query starts at t1 + (-inf) = -inf
+            // and returns the first one's hit again, so `hit1.t >= hit2.t` (volume.rs:47-49) ends it with None before any
+            // random number is drawn — and the outer `?` propagates the None.  The object still takes part in the
+            // BVH build through its bounds (volume.rs:89-93), so it is a leaf with an EMPTY boundary entry.
+            rec.entry = rec.entry_reference = REF_EMPTY_VALUE;
+        } else {
+            uint32_t bdepth = 0;
+            Built b = emit_object(v.boundary, object);
+            rec.entry_reference = make_entry(b, &bdepth);
+            rec.entry = traversal_entry(b);
+            out.max_boundary_depth = std::max(out.max_boundary_depth, std::max(bdepth, b.fast_depth + 1));
+        }
         rec.neg_inv_density = v.neg_inv_density;  // as stored by Volume::new (volume.rs:26-31)
-        rec.material = v.boundary.kind == RTR_OBJ_SPHERE ? d.spheres[v.boundary.index].material
-                                                         : d.meshes[v.boundary.index].material;
+        rec.material = geom.kind == RTR_OBJ_SPHERE ? d.spheres[geom.index].material : d.meshes[geom.index].material;
         rec.object = object;
         rec.index = ref.index;
         uint32_t vi = (uint32_t)out.volumes.size();
@@ -387,8 +397,13 @@ bool validate(const rtr_scene_desc& d, std::string& err) {
     for (uint32_t i = 0; i < d.n_objects; ++i)
         if (!ref_ok(d.objects[i], true)) return bad("object reference out of range");
     for (uint32_t i = 0; i < d.n_volumes; ++i) {
-        if (d.volumes[i].boundary.kind == RTR_OBJ_VOLUME) { err = "Volume bounded by a Volume is unsupported"; return false; }
-        if (!ref_ok(d.volumes[i].boundary, false)) return bad("volume boundary out of range");
+        // boundary: Box<dyn Object> (volume.rs:20-23) — may again be a Volume; the index-based chain must end in geometry
+        rtr_object_ref b = d.volumes[i].boundary;
+        for (uint32_t steps = 0; b.kind == RTR_OBJ_VOLUME; ++steps) {
+            if (b.index >= d.n_volumes || steps > d.n_volumes) return bad("volume boundary chain is cyclic or out of range");
+            b = d.volumes[b.index].boundary;
+        }
+        if (!ref_ok(b, false)) return bad("volume boundary out of range");
     }
     for (uint32_t i = 0; i < d.n_spheres; ++i)
         if (d.spheres[i].material >= d.n_materials) return bad("sphere material handle out of range");

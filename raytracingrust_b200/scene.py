@@ -351,9 +351,8 @@ class Scene:
                 meshes.append(ms)
                 return (A.OBJ_MESH, len(meshes) - 1)
             if isinstance(o, Volume) and allow_volume:
-                if isinstance(o.boundary, Volume):
-                    raise NotImplementedError("Volume bounded by a Volume is unsupported (RTR_UNSUPPORTED)")
-                b = lower_object(o.boundary, allow_volume=False)
+                # boundary: Box<dyn Object> (volume.rs:20-23): a Sphere, a Mesh or again a Volume
+                b = lower_object(o.boundary, allow_volume=isinstance(o.boundary, Volume))
                 volumes.append(A.VolumeS(A.ObjectRef(*b), o.neg_inv_density))
                 return (A.OBJ_VOLUME, len(volumes) - 1)
             raise TypeError(f"unknown object {o!r}")

@@ -47,8 +47,10 @@ def test_bad_handles_and_nesting_raise():
     s = rt.Scene.default()
     m = s.add_material(rt.Isotropic(rt.Color(1, 1, 1)))
     s.add_object(rt.Volume(rt.Volume(rt.Sphere(rt.Vec3(0, 0, 0), 1.0, m), 1.0), 1.0))
-    with pytest.raises(NotImplementedError):
-        s.lower()
+    low = s.lower()  # Box<dyn Object>: a Volume may bound a Volume (volume.rs:20-23)
+    assert low.desc.n_volumes == 2 and low.desc.n_objects == 1
+    outer = low.desc.volumes[low.desc.objects[0].index]
+    assert outer.boundary.kind == A.OBJ_VOLUME and low.desc.volumes[outer.boundary.index].boundary.kind == A.OBJ_SPHERE
     with pytest.raises(IndexError):
         rt.Mesh.from_buffers(np.zeros((3, 3)), np.zeros((3, 3)), [0, 1, 3], m)
     with pytest.raises(ValueError):

@@ -373,3 +373,32 @@ def test_mesh_bounded_volume_vanishes_from_outside():
     assert np.all(outside["object"] == A.RTR_NO_HIT)
     inside = o.trace_batch(rays_of([(0.1, 0.2, -5)] * k, [(0, 0, -1)] * k))
     assert (inside["object"] != A.RTR_NO_HIT).mean() > 0.95
+
+
+def test_volume_bounded_by_volume_never_hits_but_is_a_bvh_leaf():
+    """lib/volume.rs:20-23 allows any Box<dyn Object> as a boundary.  With a Volume there, the outer query
+    boundary.hit(ray, -inf, +inf) runs the inner Volume::hit with tmin = -inf: its second boundary query starts at
+    t1 + (-inf) and repeats the first, so t1 >= t2 -> None (volume.rs:36-49).  Adding such an object must not change any hit."""
+    def scene(nested):
+        s = rt.Scene.default()
+        lam = s.add_material(rt.Lambertian(rt.Color(0.5, 0.5, 0.5)))
+        iso = s.add_material(rt.Isotropic(rt.Color(1, 1, 1)))
+        s.add_object(rt.Sphere(rt.Vec3(0, -100.5, -1), 100.0, lam))
+        s.add_object(rt.Sphere(rt.Vec3(-0.6, 0, -1.2), 0.5, lam))
+        s.add_object(rt.Volume(rt.Sphere(rt.Vec3(0.7, 0.1, -1.0), 0.45, iso), 3.0))
+        if nested:
+            s.add_object(rt.Volume(rt.Volume(rt.Sphere(rt.Vec3(0, 0.3, -1.0), 0.8, iso), 5.0), 2.0))
+        return s
+    rng = np.random.default_rng(5)
+    rays = np.zeros(20000, A.RAY_DTYPE)
+    rays["origin"] = rng.uniform(-2, 2, (len(rays), 3))
+    rays["direction"] = rng.normal(size=(len(rays), 3))
+    for bvh in (True, False):
+        a = orc.OracleScene(scene(False)).trace_batch(rays, enable_bvh_tree=bvh, seed=3)
+        b = orc.OracleScene(scene(True)).trace_batch(rays, enable_bvh_tree=bvh, seed=3)
+        assert np.array_equal(a, b) and (a["object"] == 2).sum() > 100
+    # a boundary chain that loops cannot be built in Rust; through the C description it is refused
+    low = scene(True).lower()
+    low.desc.volumes[low.desc.volumes[low.desc.objects[3].index].boundary.index].boundary = A.ObjectRef(A.OBJ_VOLUME, low.desc.objects[3].index)
+    with pytest.raises(ValueError):
+        orc.OracleScene(low)
