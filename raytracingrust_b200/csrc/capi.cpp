@@ -115,6 +115,7 @@ static rtr_status context_init(rtr_context* ctx, int device, void* stream) {
         if (v >= 1024) ctx->wf_target_paths = (uint64_t)v;
     }
     if (const char* e = std::getenv("RTR_WF_GRAPH")) ctx->wf_use_graph = std::atoi(e);
+    if (const char* e = std::getenv("RTR_WF_ATOMICS")) ctx->wf_atomics_mode = (uint32_t)std::atoi(e) & 3u;
     if (const char* e = std::getenv("RTR_WF_BIN")) {  // 0 = off, 8 = octant, 24 = octant x dominant axis
         const int v = std::atoi(e);
         ctx->wf_bin_keys = v <= 0 ? 0u : v <= 8 ? 8u : 24u;
@@ -428,6 +429,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     a.k0 = (uint32_t)p->seed; a.k1 = (uint32_t)(p->seed >> 32);
     a.sample_begin = p->sample_begin; a.sample_end = p->sample_begin + count;
     a.refill_threshold = ctx->wf_refill_threshold;
+    a.atomics_mode = ctx->wf_atomics_mode;
     a.tmin = 0.00001f;  // render.rs:38
     a.accumulate = (p->flags & RTR_FLAG_ACCUMULATE) ? 1u : 0u;
     // samples of every pixel in flight per wave: enough paths to fill the chip, bounded scratch
@@ -466,7 +468,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     };
     const int ext_grid = blocks_for(n_paths * RTR_WF_THREADS / RTR_WF_EXTEND_THREADS, per_sm);
     const int gen_grid = blocks_for(n_paths + 32 * (uint64_t)ws * (W / 8 + H / 4 + 2), 16);
-    const int shade_grid = blocks_for(n_paths, 16);
+    const int shade_grid = blocks_for(n_paths * RTR_WF_THREADS / wf_shade_threads(), 16 * RTR_WF_THREADS / wf_shade_threads());
     const int sum_grid = blocks_for(n_pixels, 8);
     const int bin_grid = (int)std::min<uint64_t>((n_paths + RTR_WF_BIN_BLOCK - 1) / RTR_WF_BIN_BLOCK, (uint64_t)ctx->sm_count * 8);
     if (reset_stats) CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
@@ -684,6 +686,7 @@ rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_r
     a.k0 = (uint32_t)seed; a.k1 = (uint32_t)(seed >> 32);
     a.sample_begin = 0; a.sample_end = 1; a.wave_samples = 1;
     a.refill_threshold = ctx->wf_refill_threshold;
+    a.atomics_mode = ctx->wf_atomics_mode;
     a.tmin = tmin;
     a.in.o = ctx->wf_state; a.in.d = ctx->wf_state + piece; a.hit = ctx->wf_state + 2 * piece;
     a.counters = ctx->wf_counters;

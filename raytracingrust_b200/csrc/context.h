@@ -33,6 +33,10 @@ struct rtr_context {
     uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
     uint64_t wf_target_paths = 1ull << 24;  // RTR_WF_PATHS: paths in flight per wave (swept 2^22..2^25 on B200; 2.1 GB of path state)
     int wf_use_graph = 1;  // RTR_WF_GRAPH
+    // Same-address atomics run at ~1 per ns on B200 (ncu, profiles/r2: wf_generate issued 24 % of its slots and used 19 % of
+    // DRAM while doing 512 K atomicAdds on the queue counter in 0.48 ms).  RTR_WF_ATOMICS: bit 0 = atomic-free wf_generate
+    // when the image tiles exactly, bit 1 = one compaction atomic per CTA in wf_shade (0 = one per warp, as in round 1).
+    uint32_t wf_atomics_mode = 3;
     uint32_t wf_bin_keys = 0;  // RTR_WF_BIN: direction-binning keys of bounces >= 1 (0 = off: measured -1..-7 %; 8 = octant, 24 = octant x major axis)
     uint32_t wf_bin_last_bounce = 255;  // RTR_WF_BIN_LAST: bin bounces 1..this
     int use_scan_kernel = 1;  // RTR_SCAN_KERNEL: 0 sends all-sphere BVH-off renders through the generic megakernel

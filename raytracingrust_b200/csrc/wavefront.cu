@@ -21,8 +21,11 @@
 #include "device_core.cuh"
 #include "kernels.h"
 
+#ifndef RTR_WF_SHADE_THREADS
+#define RTR_WF_SHADE_THREADS 256  // CTA size of wf_shade = paths per compaction atomic in the per-CTA mode (A/B 128..1024: profiles/r2/ab_shade_cta.txt)
+#endif
 #ifndef RTR_WF_SHADE_MIN_BLOCKS
-#define RTR_WF_SHADE_MIN_BLOCKS 9  // wf_shade waits on memory (ncu: 3.8 long-scoreboard stalls per issue); swept 9 / 12 / 16
+#define RTR_WF_SHADE_MIN_BLOCKS 4  // wf_shade waits on memory (ncu: 3.8 long-scoreboard stalls per issue); swept 9 / 12 / 16
 #endif
 #ifndef RTR_WF_NODE_BURST
 #define RTR_WF_NODE_BURST 0  // 1: two node steps per scheduling decision
@@ -75,6 +78,11 @@ __global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArg
     const uint32_t per_sample = tiles_x * tiles_y * 32u;
     const uint64_t total = (uint64_t)per_sample * w.samples;
     const uint32_t lane = threadIdx.x & 31u;
+    // One atomicAdd per warp on the queue counter made this kernel atomic-bound (~1 same-address atomic per ns: 512 K of
+    // them for a 16 M-path wave = 0.48 ms at 24 % issue, 19 % DRAM).  When the image is a whole number of 8x4 tiles no
+    // compaction is needed at all: slot = tile-order index, the queue size is written once.
+    const bool direct = (a.atomics_mode & 1u) != 0u && (a.width & 7u) == 0u && (a.height & 3u) == 0u;
+    if (direct && blockIdx.x == 0 && threadIdx.x == 0) a.counters[WFC_QCOUNT] = a.max_ray_depth != 0u ? (uint32_t)total : 0u;
     for (uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < total;
          base += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t i = base + lane;
@@ -88,8 +96,12 @@ __global__ void __launch_bounds__(RTR_WF_THREADS) wf_generate_kernel(const WfArg
         const uint32_t m = __ballot_sync(0xffffffffu, live);
         if (m == 0u) continue;
         uint32_t slot = 0;
-        if (lane == (uint32_t)(__ffs(m) - 1)) slot = atomicAdd(&a.counters[WFC_QCOUNT], (uint32_t)__popc(m));
-        slot = __shfl_sync(0xffffffffu, slot, __ffs(m) - 1) + __popc(m & lanemask_lt());
+        if (direct) {
+            slot = (uint32_t)i;  // every lane of every tile is a pixel: the tile-order index IS the dense slot
+        } else {
+            if (lane == (uint32_t)(__ffs(m) - 1)) slot = atomicAdd(&a.counters[WFC_QCOUNT], (uint32_t)__popc(m));
+            slot = __shfl_sync(0xffffffffu, slot, __ffs(m) - 1) + __popc(m & lanemask_lt());
+        }
         if (live) {
             RngKey key; key.k0 = a.k0; key.k1 = a.k1; key.pixel = pixel; key.sample = w.begin + rel; key.bounce = 0;
             const Ray r = camera_sample_ray(a.cam, a.width, a.height, x, y, key);  // render.rs:88-92
@@ -338,15 +350,22 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
 
 // ------------------------------------------------------------------ shade + compact
 template <bool COUNT>
-__global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_SHADE_MIN_BLOCKS) wf_shade_kernel(const WfArgs a) {
+__global__ void __launch_bounds__(RTR_WF_SHADE_THREADS, RTR_WF_SHADE_MIN_BLOCKS) wf_shade_kernel(const WfArgs a) {
     const uint32_t FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = a.counters[WFC_QCOUNT + a.bounce];
     const WaveInfo w = wave_info(a);
     uint32_t* n_out = &a.counters[WFC_QCOUNT + a.bounce + 1];
     Counters cnt; cnt.nodes = cnt.tris = cnt.spheres = cnt.env = 0;
-    for (uint32_t base = (blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n; base += gridDim.x * blockDim.x) {
-        const uint32_t i = base + lane;
+    // compaction bookkeeping of the per-CTA mode (double buffered: a warp may start trip k+1 while another still reads trip k)
+    constexpr uint32_t NW = RTR_WF_SHADE_THREADS / 32;
+    __shared__ uint32_t s_cnt[2][NW];  // survivors per warp, then (after the scan) the warp's first output slot
+    const bool per_cta = (a.atomics_mode & 2u) != 0u;
+    const uint32_t warp = threadIdx.x >> 5;
+    uint32_t trip = 0;
+    // the loop is uniform per CTA (block base), so __syncthreads inside it is safe
+    for (uint32_t bb = blockIdx.x * blockDim.x; bb < n; bb += gridDim.x * blockDim.x, ++trip) {
+        const uint32_t i = bb + threadIdx.x;
         bool cont = false;
         Ray ray; ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
         v3 T = mk(0.0f, 0.0f, 0.0f);
@@ -386,7 +405,34 @@ __global__ void __launch_bounds__(RTR_WF_THREADS, RTR_WF_SHADE_MIN_BLOCKS) wf_sh
         }
         // ---- compaction: survivors go densely into the other buffer  [bucket:wf_compact]
         const uint32_t m = __ballot_sync(FULL, cont);
-        if (m != 0u) {
+        if (per_cta) {
+            // one atomicAdd on the queue counter per CTA and trip instead of one per warp (the counter is a single address:
+            // ~1 atomic per ns, and a 16 M-path bounce did 512 K of them)
+            const uint32_t buf = trip & 1u;
+            if (lane == 0) s_cnt[buf][warp] = (uint32_t)__popc(m);
+            __syncthreads();
+            if (warp == 0) {  // exclusive scan of the warps' counts, one atomicAdd for the CTA's total
+                const uint32_t c = lane < NW ? s_cnt[buf][lane] : 0u;
+                uint32_t inc = c;
+#pragma unroll
+                for (uint32_t o = 1; o < NW; o <<= 1) {
+                    const uint32_t v = __shfl_up_sync(FULL, inc, o);
+                    if (lane >= o) inc += v;
+                }
+                const uint32_t total = __shfl_sync(FULL, inc, NW - 1);
+                uint32_t cta_base = 0;
+                if (lane == 0 && total != 0u) cta_base = atomicAdd(n_out, total);
+                cta_base = __shfl_sync(FULL, cta_base, 0);
+                if (lane < NW) s_cnt[buf][lane] = cta_base + inc - c;
+            }
+            __syncthreads();
+            if (cont) {
+                const uint32_t slot = s_cnt[buf][warp] + (uint32_t)__popc(m & lanemask_lt());
+                a.out.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(pixel));
+                a.out.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float((rel << 8) | depth));
+                a.out.thr[slot] = make_float4(T.x, T.y, T.z, 0.0f);
+            }
+        } else if (m != 0u) {
             const int leader = __ffs(m) - 1;
             uint32_t slot = 0;
             if ((int)lane == leader) slot = atomicAdd(n_out, (uint32_t)__popc(m));
@@ -519,9 +565,11 @@ cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool co
     return cudaGetLastError();
 }
 
+int wf_shade_threads() { return RTR_WF_SHADE_THREADS; }
+
 cudaError_t launch_wf_shade(const WfArgs& a, int grid, bool count, cudaStream_t st) {
-    if (count) wf_shade_kernel<true><<<grid, RTR_WF_THREADS, 0, st>>>(a);
-    else wf_shade_kernel<false><<<grid, RTR_WF_THREADS, 0, st>>>(a);
+    if (count) wf_shade_kernel<true><<<grid, RTR_WF_SHADE_THREADS, 0, st>>>(a);
+    else wf_shade_kernel<false><<<grid, RTR_WF_SHADE_THREADS, 0, st>>>(a);
     return cudaGetLastError();
 }
 
