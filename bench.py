@@ -329,6 +329,11 @@ class Bench:
             torch.cuda.synchronize()
             xr_ms = e0.elapsed_time(e1) / 5
         k_ms = float(np.mean(kern_ms))
+        by_rank = [k_ms]
+        if world > 1:  # every rank's render time, so the record shows WHICH rank is slow
+            g = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(world)]
+            dist.all_gather(g, torch.tensor([k_ms], dtype=torch.float64, device="cuda"))
+            by_rank = [float(x[0]) for x in g]
         ms, rays_step = self.reduce_pair(ms, st_full["rays"])
         k_max, _ = self.reduce_pair(k_ms, 0)
         k_min = -self.reduce_pair(-k_ms, 0)[0]
@@ -422,7 +427,7 @@ class Bench:
             # our kernels per step: the render kernels (megakernel, or the wavefront's per-wave sequence) + resolve_kernel
             # (NCCL's reduce kernel is not ours)
             "gpu_launches": steps * (st_full["kernel_launches"] + 1),
-            "per_rank": {"render_ms_max": k_max, "render_ms_min": k_min, "reduce_resolve_ms": xr_ms,
+            "per_rank": {"render_ms_max": k_max, "render_ms_min": k_min, "render_ms_by_rank": by_rank, "reduce_resolve_ms": xr_ms,
                          "step_ms": ms / steps,
                          "note": "render = this rank's kernels alone (library events); reduce_resolve = ncclReduce of the fp32 "
                                  "image + resolve on rank 0, timed alone; step - render_max - reduce_resolve = launch gaps + rank skew"},
