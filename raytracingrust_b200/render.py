@@ -272,6 +272,13 @@ class DeviceScene:
                                      flags, seed, hits.ctypes.data, C.byref(st)), self.ctx._h)
         return (hits, st.as_dict()) if want_stats else hits
 
+    def trace_batch_into(self, rays_ptr, n, hits_ptr, tmin=1e-5, enable_bvh_tree=True, flags=0, seed=0):
+        """Same, with caller-owned HOST buffers (e.g. pinned): rays_ptr -> n rtr_ray, hits_ptr -> n rtr_hit.  Returns stats."""
+        st = A.Stats()
+        _check(lib().rtr_trace_batch(self.ctx._h, self._h, rays_ptr, n, tmin, int(enable_bvh_tree), flags, seed, hits_ptr,
+                                     C.byref(st)), self.ctx._h)
+        return st.as_dict()
+
     def scatter_batch(self, inp, mode=A.MODE_FULL, seed=0):
         inp = np.ascontiguousarray(inp, A.SCATTER_IN_DTYPE)
         out = np.zeros(len(inp), A.SCATTER_OUT_DTYPE)
