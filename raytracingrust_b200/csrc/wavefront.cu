@@ -18,6 +18,8 @@
 // synchronisation; capi.cpp captures it once into a CUDA graph and replays it per wave.
 // Results are bit-identical to the megakernel: the same per-path arithmetic and Philox counters, and each
 // pixel's samples are summed in sample order.
+#include <cstdlib>
+
 #include "device_core.cuh"
 #include "kernels.h"
 
@@ -537,7 +539,11 @@ static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_
 
 int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg) {
     int n = 0;
+    // RTR_WF_CARVEOUT (percent of the SM's L1/shared array given to shared memory; unset = the driver's choice): wf_extend
+    // keeps 8 KB of short stacks per CTA, the rest of the array serves node and triangle fetches as L1
+    static const int carveout = [] { const char* e = std::getenv("RTR_WF_CARVEOUT"); return e ? std::atoi(e) : -1; }();
     cudaError_t e = pick_wf_extend(exhaustive, count, volumes, tmin_arg, [&](void (*k)(const WfArgs)) {
+        if (carveout >= 0) (void)cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
         return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_WF_EXTEND_THREADS, 0);
     });
     return e == cudaSuccess ? n : 0;
