@@ -18,6 +18,7 @@
 // leaves, so ONE node array serves both the default traversal and RTR_FLAG_REFERENCE_TREE (a paired leaf is just
 // a compact encoding of the Split it replaces: one box test, then both primitives).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include <vector>
 
@@ -139,7 +140,7 @@ __global__ void k_emit_leaves(BuildArrays a, F4* spheres, PrimInfo* info, Object
     a.pmax[p] = make_float4(s.x + s.w, s.y + s.w, s.z + s.w, 0.0f);
     ObjectRec o;
     o.entry = o.entry_reference = RTR_MAKE_REF(REF_SPHERE, p);
-    o._pad[0] = o._pad[1] = 0u;
+    o.entry4 = o.entry; o._pad = 0u;
     objects[h] = o;
     linear[h] = F4{s.x, s.y, s.z, s.w};
 }
@@ -193,6 +194,46 @@ __global__ void k_emit_nodes(BuildArrays a, F4* nodes) {
     }
 }
 
+// ---- 4-wide traversal tree (flat.h nodes4) ----------------------------------------------------------------------
+// The tree's shape depends on n alone and every interior child of a Split can be replaced by its own two children
+// without overflowing four slots, so the 4-wide nodes are exactly the Splits at even depth that hold three or more
+// leaves (plus the root); each slot keeps the box its 2-wide slot carries (k_emit_nodes / child_ref).
+__global__ void k_flag4(BuildArrays a, uint32_t* flag) {
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= a.n) return;
+    flag[node] = node + 1u < a.n && (a.node_depth[node] & 1u) == 0u && (a.node_hi[node] - a.node_lo[node] >= 3u || node == 0u) ? 1u : 0u;
+}
+
+struct Slots4 { float4 mn[4], mx[4]; uint32_t ref[4]; int n; };
+__device__ __forceinline__ void slot4(const BuildArrays& a, const uint32_t* idx4, Slots4& s, uint32_t lo, uint32_t hi, uint32_t node, uint32_t parent) {
+    float4 mn, mx;
+    uint32_t ref = child_ref(a, lo, hi, node, parent, mn, mx);
+    if (RTR_REF_KIND(ref) == REF_NODE) ref = RTR_MAKE_REF(REF_NODE, idx4[node]);
+    s.mn[s.n] = mn; s.mx[s.n] = mx; s.ref[s.n] = ref; ++s.n;
+}
+__device__ __forceinline__ void expand4(const BuildArrays& a, const uint32_t* idx4, Slots4& s, uint32_t lo, uint32_t hi, uint32_t node, uint32_t parent) {
+    if (hi - lo < 3u) { slot4(a, idx4, s, lo, hi, node, parent); return; }  // a leaf or a paired leaf: one slot
+    const uint32_t mid = lo + (hi - lo) / 2u;
+    slot4(a, idx4, s, lo, mid, node + 1u, node);
+    slot4(a, idx4, s, mid, hi, node + (mid - lo), node);
+}
+__global__ void k_emit_nodes4(BuildArrays a, const uint32_t* flag, const uint32_t* idx4, F4* nodes4) {
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= a.n || flag[node] == 0u) return;
+    const uint32_t lo = a.node_lo[node], hi = a.node_hi[node], mid = lo + (hi - lo) / 2u;
+    Slots4 s;
+    s.n = 0;
+    expand4(a, idx4, s, lo, mid, node + 1u, node);
+    expand4(a, idx4, s, mid, hi, node + (mid - lo), node);
+    for (int i = s.n; i < 4; ++i) { s.mn[i] = s.mx[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); s.ref[i] = REF_EMPTY_VALUE; }
+    F4* q = nodes4 + (size_t)idx4[node] * 8;
+    for (int i = 0; i < 4; ++i) {
+        q[2 * i] = F4{s.mn[i].x, s.mn[i].y, s.mn[i].z, 0.0f};
+        q[2 * i + 1] = F4{s.mx[i].x, s.mx[i].y, s.mx[i].z, 0.0f};
+    }
+    for (int i = 0; i < 4; ++i) q[i].w = __uint_as_float(s.ref[i]);  // flat.h: the refs live in q0.w .. q3.w
+}
+
 }  // namespace
 
 bool device_build_applies(const rtr_scene_desc& d) {
@@ -203,7 +244,8 @@ bool device_build_applies(const rtr_scene_desc& d) {
     return true;
 }
 
-cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs) {
+cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs,
+                                         bool want_nodes4) {
     const uint32_t n = d.n_objects;
     cudaError_t e = cudaSuccess;
     std::vector<void*> scratch;
@@ -281,10 +323,39 @@ cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t s
     for (uint32_t L = levels; L-- > 0 && e == cudaSuccess;) k_node_boxes<<<grid, 256, 0, st>>>(a, L);
     k_emit_nodes<<<grid, 256, 0, st>>>(a, out->nodes);
     step(cudaGetLastError());
+    // 4-wide tree: flag its nodes, number them in pre-order; the count comes back with the NaN flag (one synchronisation)
+    uint32_t* flag4 = nullptr;
+    uint32_t* idx4 = nullptr;
+    if (want_nodes4 && e == cudaSuccess) {
+        flag4 = (uint32_t*)alloc((size_t)n * 4, false);
+        idx4 = (uint32_t*)alloc((size_t)n * 4 + 4, false);
+        size_t scan_bytes = 0;
+        step(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, flag4, idx4, (int)n, st));
+        void* scan_temp = alloc(scan_bytes, false);
+        if (e == cudaSuccess) {
+            k_flag4<<<grid, 256, 0, st>>>(a, flag4);
+            step(cub::DeviceScan::ExclusiveSum(scan_temp, scan_bytes, flag4, idx4, (int)n, st));
+        }
+    }
     uint32_t h_flags[4] = {0, 0, 0, 0};
+    uint32_t h_last[2] = {0, 0};  // flag and exclusive index of the last Split (node n-2): their sum is the node count
     step(cudaMemcpyAsync(h_flags, a.flags, 16, cudaMemcpyDeviceToHost, st));
+    if (idx4 && e == cudaSuccess) {
+        step(cudaMemcpyAsync(&h_last[0], flag4 + (n - 2u), 4, cudaMemcpyDeviceToHost, st));
+        step(cudaMemcpyAsync(&h_last[1], idx4 + (n - 2u), 4, cudaMemcpyDeviceToHost, st));
+    }
     step(cudaStreamSynchronize(st));
-    cleanup();
+    if (idx4 && e == cudaSuccess) {
+        out->n_nodes4 = h_last[0] + h_last[1];
+        out->nodes4 = (F4*)alloc((size_t)out->n_nodes4 * 8 * sizeof(F4), true);
+        if (e == cudaSuccess) {
+            k_emit_nodes4<<<grid, 256, 0, st>>>(a, flag4, idx4, out->nodes4);
+            step(cudaGetLastError());
+            out->root_entry4 = RTR_MAKE_REF(REF_NODE, 0u);
+            out->max_depth4 = levels / 2u + 2u;
+        }
+    }
+    cleanup();  // stream-ordered frees: after the kernel above
     out->nan_centroid = h_flags[0] != 0;
     out->n_nodes = n;
     out->root_entry = RTR_MAKE_REF(REF_NODE, n - 1u);

@@ -18,6 +18,8 @@ struct DeviceBvh {
     PrimInfo* sphere_info = nullptr;
     ObjectRec* objects = nullptr;
     F4* linear_spheres = nullptr;  // the spheres in Scene.objects order (BVH-off scan)
+    F4* nodes4 = nullptr;       // the 4-wide traversal tree (flat.h), when asked for: every other level of `nodes` folded away
+    uint32_t n_nodes4 = 0, root_entry4 = 0xFFFFFFFFu, max_depth4 = 0;
     uint32_t n_nodes = 0, root_entry = 0xFFFFFFFFu, max_depth = 0;
     uint64_t device_bytes = 0, h2d_bytes = 0;
     bool nan_centroid = false;
@@ -28,7 +30,8 @@ bool device_build_applies(const rtr_scene_desc& d);
 
 // Builds the reference tree (bvh.rs:59-144) for Scene.objects on `st`.  The four result arrays are cudaMalloc'ed
 // and appended to `allocs` (owned by the caller); scratch is freed before returning.  Synchronises `st`.
-cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs);
+cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs,
+                                         bool want_nodes4 = false);
 
 }  // namespace rtr
 #endif

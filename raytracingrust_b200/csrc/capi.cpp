@@ -120,6 +120,7 @@ static rtr_status context_init(rtr_context* ctx, int device, void* stream) {
         const int v = std::atoi(e);
         ctx->wf_bin_keys = v <= 0 ? 0u : v <= 8 ? 8u : 24u;
     }
+    if (const char* e = std::getenv("RTR_WF_WIDE")) ctx->wf_wide4 = std::atoi(e) != 0;
     if (const char* e = std::getenv("RTR_WF_BIN_LAST")) ctx->wf_bin_last_bounce = (uint32_t)std::max(0, std::atoi(e));
     if (const char* e = std::getenv("RTR_SCAN_KERNEL")) ctx->use_scan_kernel = std::atoi(e);
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
@@ -234,6 +235,8 @@ rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedS
         if (need <= stack_limit()) break;
         if (attempt == 1) return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack even when balanced");
     }
+    // the 4-wide tree pushes up to three siblings per level; a scene whose worst case would not fit keeps the 2-wide walk
+    if (3u * out.flat.max_depth4 + 4u > stack_limit()) { out.flat.nodes4.clear(); out.flat.root_entry4 = 0xFFFFFFFFu; }
     out.host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return RTR_OK;
 }
@@ -254,6 +257,7 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     cudaError_t e = cudaSuccess;
     auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
     step(upload(s, flat.nodes, &v.nodes, ctx->stream));
+    if (!flat.nodes4.empty() && ctx->wf_wide4) step(upload(s, flat.nodes4, &v.nodes4, ctx->stream));
     step(upload(s, flat.spheres, &v.spheres, ctx->stream));
     step(upload(s, flat.sphere_info, &v.sphere_info, ctx->stream));
     step(upload(s, flat.tris, &v.tris, ctx->stream));
@@ -286,6 +290,7 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     }
     v.background = flat.background;
     v.root_entry = flat.root_entry;
+    v.root_entry4 = flat.root_entry4;
     s->root_entry_reference = flat.root_entry_reference;
     v.n_objects = (uint32_t)flat.objects.size();
     v.n_materials = (uint32_t)flat.materials.size();
@@ -309,13 +314,14 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     }
     if (on_device) {
         DeviceBvh bvh;
-        cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, ctx->pool, &bvh, s->allocs);
+        cudaError_t be = build_sphere_scene_on_device(*desc, ctx->stream, ctx->pool, &bvh, s->allocs, ctx->wf_wide4 != 0u);
         if (be != cudaSuccess) { rtr_scene_destroy(s); return cuda_fail(ctx, be, "device BVH build"); }
         if (bvh.nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
         if (bvh.max_depth + 2 > stack_limit()) { rtr_scene_destroy(s); return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack"); }
         v.nodes = bvh.nodes; v.spheres = bvh.spheres; v.sphere_info = bvh.sphere_info; v.objects = bvh.objects;
         v.linear_spheres = bvh.linear_spheres;
         v.root_entry = bvh.root_entry; s->root_entry_reference = bvh.root_entry;
+        if (bvh.nodes4 && 3u * bvh.max_depth4 + 4u <= stack_limit()) { v.nodes4 = bvh.nodes4; v.root_entry4 = bvh.root_entry4; }
         v.n_objects = desc->n_objects; v.n_nodes = bvh.n_nodes; v.n_sphere_slots = desc->n_objects;
         s->n_nodes = bvh.n_nodes; s->max_depth = bvh.max_depth;
         s->device_bytes += bvh.device_bytes; s->h2d_bytes += bvh.h2d_bytes;
@@ -459,7 +465,7 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     a.accum = accum_dev;
     a.counters = ctx->wf_counters;
     a.stats = ctx->stats;
-    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u);
+    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u, false, wf_extend_wide4(a, exhaustive, count_work));
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
     auto blocks_for = [&](uint64_t items, int cap_per_sm) {
         uint64_t b = (items + RTR_WF_THREADS - 1) / RTR_WF_THREADS;
@@ -691,7 +697,7 @@ rtr_status rtr_trace_batch(rtr_context* ctx, const rtr_scene* scene, const rtr_r
     a.in.o = ctx->wf_state; a.in.d = ctx->wf_state + piece; a.hit = ctx->wf_state + 2 * piece;
     a.counters = ctx->wf_counters;
     a.stats = ctx->stats;
-    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || enable_bvh_tree == 0u, tmin != 0.00001f);
+    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || enable_bvh_tree == 0u, tmin != 0.00001f, wf_extend_wide4(a, exhaustive, count_work));
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
     CU(cudaMemcpyAsync(ctx->batch_in, rays, n * sizeof(rtr_ray), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));

@@ -37,6 +37,7 @@ struct rtr_context {
     // DRAM while doing 512 K atomicAdds on the queue counter in 0.48 ms).  RTR_WF_ATOMICS: bit 0 = atomic-free wf_generate
     // when the image tiles exactly, bit 1 = one compaction atomic per CTA in wf_shade (0 = one per warp, as in round 1).
     uint32_t wf_atomics_mode = 3;
+    uint32_t wf_wide4 = 1;     // RTR_WF_WIDE (0 = off): scenes uploaded through this context also get the 4-wide traversal tree (flat.h) and wf_extend walks it
     uint32_t wf_bin_keys = 0;  // RTR_WF_BIN: direction-binning keys of bounces >= 1 (0 = off: measured -1..-7 %; 8 = octant, 24 = octant x major axis)
     uint32_t wf_bin_last_bounce = 255;  // RTR_WF_BIN_LAST: bin bounces 1..this
     int use_scan_kernel = 1;  // RTR_SCAN_KERNEL: 0 sends all-sphere BVH-off renders through the generic megakernel

@@ -339,6 +339,40 @@ __device__ __forceinline__ void node_step(const SceneView& sc, uint32_t& cur, in
     }
 }
 
+// 4-wide node step (flat.h: nodes4).  [bucket:node_step]  One 128-B fetch, four slab tests — each against the very box the
+// 2-wide traversal tree tests for that slot, so the set of leaves reached is the same — then the pierced children are
+// ordered by entry distance with a 5-exchange network: the nearest becomes `cur`, the others go onto the stack far to
+// near.  Visiting order is a speed matter only (offer() breaks ties by DFS rank, culling keeps its slack).
+__device__ __forceinline__ void order2(float& ea, uint32_t& ra, float& eb, uint32_t& rb) {
+    const bool sw = eb < ea;
+    const float e0 = sw ? eb : ea, e1 = sw ? ea : eb;
+    const uint32_t r0 = sw ? rb : ra, r1 = sw ? ra : rb;
+    ea = e0; eb = e1; ra = r0; rb = r1;
+}
+template <typename STACK>
+__device__ __forceinline__ void node4_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
+                                           const RayInv& inv, float tmin, float tmax, const STACK& stack, int floor = 0) {
+    const F4* q = sc.nodes4 + (size_t)RTR_REF_INDEX(cur) * 8;
+    float4 q0, q1, q2, q3, q4, q5, q6, q7;
+    ldg8(q, q0, q1); ldg8(q + 2, q2, q3); ldg8(q + 4, q4, q5); ldg8(q + 6, q6, q7);
+    uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w), r2 = __float_as_uint(q2.w), r3 = __float_as_uint(q3.w);
+    const float lim = cull_limit(best.t);
+    float e0, e1, e2, e3;
+    const bool h0 = slab(q0, q1, r, inv, tmin, tmax, e0) && r0 != REF_EMPTY_VALUE && !(e0 > lim);
+    const bool h1 = slab(q2, q3, r, inv, tmin, tmax, e1) && r1 != REF_EMPTY_VALUE && !(e1 > lim);
+    const bool h2 = slab(q4, q5, r, inv, tmin, tmax, e2) && r2 != REF_EMPTY_VALUE && !(e2 > lim);
+    const bool h3 = slab(q6, q7, r, inv, tmin, tmax, e3) && r3 != REF_EMPTY_VALUE && !(e3 > lim);
+    const int n = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+    if (n == 0) { cur = pop_next<false>(stack, sp, best.t, floor); return; }
+    // a pierced box has a finite entry (or -inf under a -inf tmin): +inf sorts the others behind every pierced one
+    e0 = h0 ? e0 : RTR_INF; e1 = h1 ? e1 : RTR_INF; e2 = h2 ? e2 : RTR_INF; e3 = h3 ? e3 : RTR_INF;
+    order2(e0, r0, e1, r1); order2(e2, r2, e3, r3); order2(e0, r0, e2, r2); order2(e1, r1, e3, r3); order2(e1, r1, e2, r2);
+    if (n > 3) { stack.put(sp, r3, e3); ++sp; }
+    if (n > 2) { stack.put(sp, r2, e2); ++sp; }
+    if (n > 1) { stack.put(sp, r1, e1); ++sp; }
+    cur = r0;
+}
+
 // [bucket:leaf_step]
 // the primitive test of a leaf step, without the pop: `cur` is read only
 template <bool EXHAUSTIVE, bool COUNT, bool NESTED, bool VOLUMES = true, typename STACK>

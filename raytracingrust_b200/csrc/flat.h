@@ -37,6 +37,13 @@ enum : uint32_t {
 #define RTR_MAKE_REF(kind, idx) (((uint32_t)(kind) << 29) | (uint32_t)(idx))
 static const uint32_t REF_EMPTY_VALUE = 0xFFFFFFFFu;  // kind 7
 
+// 4-wide traversal node (128 B, 128-B aligned, 8 x float4), host-built scenes only: the SAH traversal tree with every
+// other level folded away.  Child k's box is the SAME box its slot carries in the 2-wide tree (an interior box is a
+// union of gates, a leaf slot carries its gate), so the candidate set — every leaf whose gate is pierced — is unchanged:
+//   q0 = { c0.min, bits(ref0) }  q1 = { c0.max, bits(ref1) }  q2 = { c1.min, bits(ref2) }  q3 = { c1.max, bits(ref3) }
+//   q4 = { c2.min, 0 }           q5 = { c2.max, 0 }           q6 = { c3.min, 0 }           q7 = { c3.max, 0 }
+// REF_NODE references inside nodes4 index nodes4; unused slots hold REF_EMPTY.  Only the 4-wide instantiation of wf_extend
+// walks it (SceneView::root_entry4, VolumeRec::entry4, ObjectRec::entry4); every other walk uses the 2-wide arrays.
 struct F4 { float x, y, z, w; };
 struct U4 { uint32_t x, y, z, w; };
 
@@ -54,13 +61,14 @@ struct VolumeRec {        // Volume (lib/volume.rs:19-31)
     uint32_t rank;        // DFS leaf rank of the volume leaf
     uint32_t index;       // index in rtr_scene_desc.volumes (RNG iteration slot)
     uint32_t entry_reference;  // the boundary in the reference topology (RTR_FLAG_REFERENCE_TREE)
-    uint32_t _pad;
+    uint32_t entry4;      // the boundary in the 4-wide traversal tree (REF_NODE -> nodes4), or the same leaf ref
 };
 
 struct ObjectRec {        // Scene.objects[i], for the BVH-off linear scan (scene.rs:141-156)
     uint32_t entry;       // SPHERE slot | NODE (pseudo parent) | TRI | VOLUME | EMPTY
     uint32_t entry_reference;  // the same in the reference topology
-    uint32_t _pad[2];
+    uint32_t entry4;      // the same in the 4-wide traversal tree
+    uint32_t _pad;
 };
 
 struct MaterialRec {      // Box<dyn Material>
@@ -81,6 +89,9 @@ struct BackgroundRec {
 // Device view: raw pointers into one allocation each.
 struct SceneView {
     const F4* nodes;          // 4 per node
+    const F4* nodes4;         // 8 per 4-wide node (null: the scene has no 4-wide tree, e.g. it was built on the device)
+    uint32_t root_entry4;     // entry ref of the 4-wide traversal tree
+    uint32_t _pad4;
     const F4* spheres;        // (cx, cy, cz, r) per slot
     const PrimInfo* sphere_info;
     const F4* tris;           // 4 per slot (64 B, one aligned record = two 256-bit loads): (v0.xyz, fn.x) (e1.xyz, fn.y)

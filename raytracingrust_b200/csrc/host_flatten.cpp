@@ -328,6 +328,61 @@ struct Flattener {
         return RTR_MAKE_REF(REF_NODE, idx);
     }
 
+    // ---- 4-wide traversal tree (flat.h) ------------------------------------------------------------------
+    // Folds the 2-wide traversal tree below `entry`: a node takes its two child slots and, while it has a free slot,
+    // replaces the interior child with the largest box by that child's own two slots (single-child pseudo parents are
+    // looked through).  Each slot keeps the box the 2-wide tree tests for it.  Returns the 4-wide ref (a leaf ref as is).
+    struct Slot { uint32_t ref; Box box; };
+    void slots_of(uint32_t node, std::vector<Slot>& out) const {  // the (at most two) child slots of a 2-wide node
+        const F4* q = &this->out.nodes[(size_t)node * 4];
+        uint32_t l, r;
+        std::memcpy(&l, &q[0].w, 4); std::memcpy(&r, &q[1].w, 4);
+        if (l != REF_EMPTY_VALUE) out.push_back(Slot{l, Box{V3{q[0].x, q[0].y, q[0].z}, V3{q[1].x, q[1].y, q[1].z}}});
+        if (r != REF_EMPTY_VALUE) out.push_back(Slot{r, Box{V3{q[2].x, q[2].y, q[2].z}, V3{q[3].x, q[3].y, q[3].z}}});
+    }
+    uint32_t collapse4(uint32_t entry, uint32_t* depth) {
+        if (entry == REF_EMPTY_VALUE || RTR_REF_KIND(entry) != REF_NODE) { *depth = entry == REF_EMPTY_VALUE ? 0u : 1u; return entry; }
+        std::vector<Slot> s;
+        slots_of(RTR_REF_INDEX(entry), s);
+        for (;;) {
+            int pick = -1;
+            float best = -1.0f;
+            for (size_t i = 0; i < s.size(); ++i) {
+                if (RTR_REF_KIND(s[i].ref) != REF_NODE) continue;
+                std::vector<Slot> kids;
+                slots_of(RTR_REF_INDEX(s[i].ref), kids);
+                if (kids.size() <= 1) { pick = (int)i; break; }  // a single-child pseudo parent costs no slot: look through it
+                if (s.size() + 1 > 4) continue;
+                const float area = half_area(s[i].box);
+                if (area > best) { pick = (int)i; best = area; }  // else: the largest interior box that still fits
+            }
+            if (pick < 0) break;
+            std::vector<Slot> kids;
+            slots_of(RTR_REF_INDEX(s[pick].ref), kids);
+            s.erase(s.begin() + pick);
+            s.insert(s.begin() + pick, kids.begin(), kids.end());
+        }
+        const uint32_t idx = (uint32_t)(out.nodes4.size() / 8);
+        out.nodes4.resize(out.nodes4.size() + 8, F4{0, 0, 0, 0});
+        uint32_t refs[4] = {REF_EMPTY_VALUE, REF_EMPTY_VALUE, REF_EMPTY_VALUE, REF_EMPTY_VALUE};
+        Box boxes[4] = {};
+        uint32_t deepest = 0;
+        for (size_t i = 0; i < s.size(); ++i) {
+            uint32_t d = 0;
+            refs[i] = collapse4(s[i].ref, &d);  // recursion may grow nodes4: index, never hold pointers across it
+            boxes[i] = s[i].box;
+            deepest = std::max(deepest, d);
+        }
+        F4* q = &out.nodes4[(size_t)idx * 8];
+        for (int i = 0; i < 4; ++i) {
+            q[2 * i] = F4{boxes[i].min.x, boxes[i].min.y, boxes[i].min.z, 0.0f};
+            q[2 * i + 1] = F4{boxes[i].max.x, boxes[i].max.y, boxes[i].max.z, 0.0f};
+        }
+        q[0].w = bits(refs[0]); q[1].w = bits(refs[1]); q[2].w = bits(refs[2]); q[3].w = bits(refs[3]);
+        *depth = deepest + 1;
+        return RTR_MAKE_REF(REF_NODE, idx);
+    }
+
     // ---- leaves -------------------------------------------------------------
     Built emit_sphere(uint32_t sphere_index, uint32_t object) {
         const rtr_sphere& s = d.spheres[sphere_index];
@@ -515,12 +570,22 @@ int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint
 
     // linear-scan table (scene.rs:141-156): one entry per object, in add_object order.  A mesh
     // root that is a Split needs its own box tested on entry -> pseudo parent per mesh object.
+    uint32_t v_depth4 = 0;
     out.objects.resize(d.n_objects);
     for (uint32_t i = 0; i < d.n_objects; ++i) {
         std::memset(&out.objects[i], 0, sizeof(ObjectRec));
         uint32_t dd = 0;
         out.objects[i].entry_reference = f.make_entry(coll.built[i], &dd);
         out.objects[i].entry = f.traversal_entry(coll.built[i]);
+    }
+    // 4-wide traversal trees of the scene, of every volume boundary and of every object (linear scan entries)
+    {
+        uint32_t d4 = 0;
+        out.root_entry4 = f.collapse4(out.root_entry, &d4);
+        out.max_depth4 = d4;
+        for (VolumeRec& v : out.volumes) { v.entry4 = f.collapse4(v.entry, &d4); v_depth4 = std::max(v_depth4, d4); }
+        for (ObjectRec& o : out.objects) { o.entry4 = f.collapse4(o.entry, &d4); out.max_depth4 = std::max(out.max_depth4, d4); }
+        out.max_depth4 += v_depth4;  // a boundary walk is stacked on top of the suspended scene walk
     }
     out.materials.resize(d.n_materials);
     for (uint32_t i = 0; i < d.n_materials; ++i) {

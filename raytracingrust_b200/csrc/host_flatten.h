@@ -12,6 +12,9 @@ namespace rtr {
 
 struct HostFlat {
     std::vector<F4> nodes, spheres, tris, tri_vn, env;
+    std::vector<F4> nodes4;                       // 4-wide traversal tree (flat.h), 8 per node; empty when not built
+    uint32_t root_entry4 = 0xFFFFFFFFu;
+    uint32_t max_depth4 = 0;                      // deepest root-to-leaf path of any 4-wide tree (stack need: 3 per level)
     std::vector<PrimInfo> sphere_info, tri_info;
     std::vector<VolumeRec> volumes;
     std::vector<ObjectRec> objects;

@@ -98,6 +98,12 @@ cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, u
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS
 #define RTR_WF_EXTEND_MIN_BLOCKS 8  // wf_extend with Volume::hit compiled in (64 registers)
 #endif
+#ifndef RTR_WF_EXTEND_MIN_BLOCKS_W4
+#define RTR_WF_EXTEND_MIN_BLOCKS_W4 8        // the 4-wide instantiations (swept 6..8 with Volume::hit, 7..9 without: profiles/r2/ab_bvh4_variants.txt)
+#endif
+#ifndef RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4
+#define RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4 8
+#endif
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS_NOVOL
 #define RTR_WF_EXTEND_MIN_BLOCKS_NOVOL 9  // without it: 56 registers, swept 6..10 on B200 (9: +2..5 % over 8)
 #endif
@@ -139,7 +145,8 @@ struct WfArgs {
     uint32_t bin_keys;                  // 8: direction octant; 24: octant x dominant axis
 };
 
-int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg = false);
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg = false, bool wide4 = false);
+bool wf_extend_wide4(const WfArgs& a, bool exhaustive, bool count);  // will launch_wf_extend walk the 4-wide tree for these arguments?
 cudaError_t launch_wf_begin(const WfArgs& a, cudaStream_t st);       // zero accum + wave counter
 cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st);
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);

@@ -84,7 +84,7 @@ extern "C" rtr_status rtr_trace_batch_device_noalloc(rtr_context* ctx, const rtr
     a.stats = reinterpret_cast<unsigned long long*>(base + WFC_WORDS * sizeof(uint32_t));
     float4* streams = reinterpret_cast<float4*>(base + kHeaderBytes);
     a.in.o = streams; a.in.d = streams + kMaxRays; a.hit = streams + 2 * kMaxRays;
-    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || enable_bvh_tree == 0u, tmin != 0.00001f);
+    const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || enable_bvh_tree == 0u, tmin != 0.00001f, wf_extend_wide4(a, exhaustive, count_work));
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
     // the array keeps the previous call's queue size and fetch position: both must start at zero
     CU(cudaMemsetAsync(base, 0, kHeaderBytes, ctx->stream));

@@ -191,8 +191,10 @@ __global__ void __launch_bounds__(256) wf_bin_kernel(const WfArgs a) {
 // and the per-ray RNG key from the traversal state (ncu: local-memory traffic was 44 % of wf_extend's L1 wavefronts).
 // TMIN_ARG = true: world.hit's tmin comes from the arguments (rtr_trace_batch with a tmin other than render()'s 1e-5);
 // the render path keeps the literal, which costs the volume instantiation 30 bytes of spills less.
-template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES, bool TMIN_ARG = false>
-__global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL) wf_extend_kernel(const WfArgs a) {
+// WIDE4 = true: interior steps walk the 4-wide tree (flat.h: nodes4, node4_step); culled, non-counting, render-tmin walks only.
+template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES, bool TMIN_ARG = false, bool WIDE4 = false>
+__global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, WIDE4 ? (VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS_W4 : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4)
+                                                               : (VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL)) wf_extend_kernel(const WfArgs a) {
     const float tmin0 = TMIN_ARG ? a.tmin : 0.00001f;  // render.rs:38
     StackEntry stack[RTR_STACK_CAP];  // spill area of the short stack + scratch of nested (volume boundary) walks
     __shared__ uint2 short_stack[RTR_SHORT_STACK][RTR_WF_EXTEND_THREADS];
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                         }
                         inv.ix = 1.0f / r.d.x; inv.iy = 1.0f / r.d.y; inv.iz = 1.0f / r.d.z;
                         best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
-                        cur = walk_entry(a.sc.root_entry);
+                        cur = walk_entry(WIDE4 ? a.sc.root_entry4 : a.sc.root_entry);
                         sp = 0;
                         if (VOLUMES) { vstate = 0u; floor = 0; tmin_cur = tmin0; }
                         has = true;
@@ -270,7 +272,9 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                     const uint32_t mn = __ballot_sync(FULL, at_node);
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
-                    if (at_node) {
+                    if (at_node && WIDE4) {
+                        node4_step(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, VOLUMES ? floor : 0);
+                    } else if (at_node) {
                         node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
 #if RTR_WF_NODE_BURST
                         if (RTR_REF_KIND(cur) == REF_NODE) node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
@@ -281,7 +285,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                     if (VOLUMES && RTR_REF_KIND(cur) == REF_VOLUME && vstate == 0u) {  // [bucket:volume_fsm]
                         const uint32_t vidx = RTR_REF_INDEX(cur);
                         const VolumeRec& vol = a.sc.volumes[vidx];
-                        const uint32_t entry = walk_entry(a.sc.reference_tree ? vol.entry_reference : vol.entry);
+                        const uint32_t entry = walk_entry(WIDE4 ? vol.entry4 : a.sc.reference_tree ? vol.entry_reference : vol.entry);
                         if (entry == RTR_REF_DONE) {  // empty boundary: Volume::hit is None
                             cur = pop_next<EXHAUSTIVE>(wstack, sp, best.t, 0);
                         } else {  // suspend the outer walk, start boundary.hit(ray, -inf, +inf)  (volume.rs:36)
@@ -309,7 +313,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, VOLUMES ? RTR_WF_EXTEND
                         vstate = (2u << 30) | vidx;
                         tmin_cur = t1 + tmin0;
                         best.t = RTR_INF; best.ref = REF_EMPTY_VALUE; best.u = best.v = 0.0f;
-                        cur = walk_entry(a.sc.reference_tree ? vol.entry_reference : vol.entry);
+                        cur = walk_entry(WIDE4 ? vol.entry4 : a.sc.reference_tree ? vol.entry_reference : vol.entry);
                     } else {
                         float t_hit = __int_as_float(0x7fc00000);  // None
                         int base = floor;                          // stack level of the saved outer hit + 2
@@ -525,7 +529,11 @@ cudaError_t launch_trace_finish(const WfArgs& a, uint32_t n, rtr_hit* out, cudaS
 
 // ------------------------------------------------------------------ launchers
 template <typename F>
-static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_arg, F f) {
+static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_arg, bool wide4, F f) {
+    if (wide4 && !exhaustive && !count && !tmin_arg) {
+        if (volumes) return f(wf_extend_kernel<false, false, true, false, true>);
+        return f(wf_extend_kernel<false, false, false, false, true>);
+    }
 #define RTR_PICK(E, C, V) do { if (tmin_arg) return f(wf_extend_kernel<E, C, V, true>); return f(wf_extend_kernel<E, C, V, false>); } while (0)
     if (exhaustive) {
         if (count) { if (volumes) RTR_PICK(true, true, true); else RTR_PICK(true, true, false); }
@@ -537,12 +545,16 @@ static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_
 #undef RTR_PICK
 }
 
-int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg) {
+bool wf_extend_wide4(const WfArgs& a, bool exhaustive, bool count) {
+    return a.sc.nodes4 != nullptr && a.sc.reference_tree == 0u && a.enable_bvh_tree != 0u && !exhaustive && !count && a.tmin == 0.00001f;
+}
+
+int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg, bool wide4) {
     int n = 0;
     // RTR_WF_CARVEOUT (percent of the SM's L1/shared array given to shared memory; unset = the driver's choice): wf_extend
     // keeps 8 KB of short stacks per CTA, the rest of the array serves node and triangle fetches as L1
     static const int carveout = [] { const char* e = std::getenv("RTR_WF_CARVEOUT"); return e ? std::atoi(e) : -1; }();
-    cudaError_t e = pick_wf_extend(exhaustive, count, volumes, tmin_arg, [&](void (*k)(const WfArgs)) {
+    cudaError_t e = pick_wf_extend(exhaustive, count, volumes, tmin_arg, wide4, [&](void (*k)(const WfArgs)) {
         if (carveout >= 0) (void)cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);
         return cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k, RTR_WF_EXTEND_THREADS, 0);
     });
@@ -564,7 +576,7 @@ cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool co
     // the generic instantiation also carries the BVH-off linear scan
     const bool volumes = a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u;
     const bool tmin_arg = a.tmin != 0.00001f;
-    pick_wf_extend(exhaustive, count, volumes, tmin_arg, [&](void (*k)(const WfArgs)) {
+    pick_wf_extend(exhaustive, count, volumes, tmin_arg, wf_extend_wide4(a, exhaustive, count), [&](void (*k)(const WfArgs)) {
         k<<<grid, RTR_WF_EXTEND_THREADS, 0, st>>>(a);
         return cudaSuccess;
     });

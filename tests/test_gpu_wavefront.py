@@ -106,6 +106,49 @@ def test_wavefront_zero_sized_and_empty(ctx):
         assert rgba.size == 0 and st["rays"] == 0
 
 
+def _context_with(env):
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        return rt.Context(0)  # the knobs are read when the context is created
+    finally:
+        for k, v in old.items():
+            os.environ.pop(k) if v is None else os.environ.__setitem__(k, v)
+
+
+@pytest.mark.parametrize("name,W,H,spp", [("mesh_hdri", 1280, 720, 2), ("volumes", 1280, 720, 2), ("nested_volumes", 1024, 1024, 2),
+                                          ("spheres_host_built", 1280, 720, 2), ("spheres_device_built", 1280, 720, 2),
+                                          ("grid_depth50", 1024, 768, 2)])
+def test_four_wide_walk_is_bit_identical_to_the_two_wide_walk(name, W, H, spp):
+    """wf_extend walks the 4-wide traversal tree by default (flat.h nodes4; RTR_WF_WIDE=0 keeps the 2-wide tree).  Both
+    test the same gate boxes, so images, ray counts and closest-hit batches must not differ by a bit."""
+    from test_gpu_edge import nested_volume_scene
+    env = {}
+    if name == "mesh_hdri": scene = _scenes.mesh_hdri(256, 128)
+    elif name == "volumes": scene = _scenes.volumes(128, 64)
+    elif name == "nested_volumes": scene = nested_volume_scene()
+    elif name == "grid_depth50": scene = _scenes.grid_spheres(10)
+    else:
+        scene = _scenes.random_spheres(30_000)
+        env = {"RTR_BVH_BUILD": "host" if name == "spheres_host_built" else "device"}
+    scene.settings.samples_per_pixel = spp
+    rays = _scenes.camera_rays_np(scene, 320, 200, seed=3)
+    out = []
+    for wide in ("1", "0"):
+        c = _context_with(dict(env, RTR_WF_WIDE=wide))
+        try:
+            ds = c.upload(scene)
+            rgba, acc, st = ds.render(wf(scene, W, H, seed=5), want_accum=True)
+            assert st["kernel_used"] == A.KERNEL_WAVEFRONT
+            out.append((rgba, acc, st["rays"], ds.trace_batch(rays, seed=5)))
+        finally:
+            c.close()
+    (rgba4, acc4, rays4, hits4), (rgba2, acc2, rays2, hits2) = out
+    assert rays4 == rays2 and np.array_equal(acc4, acc2) and np.array_equal(rgba4, rgba2)
+    assert hits4.tobytes() == hits2.tobytes()
+    assert (hits4["object"] != A.RTR_NO_HIT).mean() > 0.05
+
+
 def test_auto_kernel_choice(ctx):
     """RTR_KERNEL_AUTO: wavefront for BVH walks big enough to fill a wave, megakernel otherwise (capi.cpp)."""
     mesh = _scenes.mesh_hdri(64, 32)
