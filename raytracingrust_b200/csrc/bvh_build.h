@@ -9,6 +9,7 @@
 
 #include "../../include/rtr.h"
 #include "flat.h"
+#include "host_flatten.h"
 
 namespace rtr {
 
@@ -32,6 +33,12 @@ bool device_build_applies(const rtr_scene_desc& d);
 // and appended to `allocs` (owned by the caller); scratch is freed before returning.  Synchronises `st`.
 cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t st, cudaMemPool_t pool, DeviceBvh* out, std::vector<void*>& allocs,
                                          bool want_nodes4 = false);
+
+// mesh.build_bvh() (mesh.rs:119-121) of one mesh on `st`: writes the mesh's node, 4-wide node (nodes4 may be null) and
+// triangle records into the ranges `dm` reserves in the scene's device arrays.  Scratch and the device copies of the vertex
+// buffers come from `pool` and are freed before returning.  Synchronises `st`.
+cudaError_t build_mesh_on_device(const rtr_mesh& mesh, const DeviceMesh& dm, cudaStream_t st, cudaMemPool_t pool, F4* nodes, F4* nodes4,
+                                 F4* tris, F4* tri_vn, uint64_t* h2d_bytes, bool* nan_centroid, bool* count_mismatch);
 
 }  // namespace rtr
 #endif

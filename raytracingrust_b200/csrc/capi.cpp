@@ -175,9 +175,10 @@ rtr_status rtr_synchronize(rtr_context* ctx) {
 
 // ------------------------------------------------------------------ scene upload
 template <typename T>
-static cudaError_t upload(rtr_scene* s, const std::vector<T>& v, const T** dst, cudaStream_t st) {
+static cudaError_t upload(rtr_scene* s, const std::vector<T>& v, const T** dst, cudaStream_t st, size_t prefix = 0) {
+    // `prefix` elements are left in front of the host data for records written on the device
     *dst = nullptr;
-    size_t bytes = v.size() * sizeof(T);
+    size_t bytes = (prefix + v.size()) * sizeof(T);
     if (bytes == 0) bytes = sizeof(T);  // keep pointers valid
     void* p = nullptr;
     cudaError_t e = cudaMallocFromPoolAsync(&p, bytes, s->ctx->pool, st);
@@ -185,7 +186,7 @@ static cudaError_t upload(rtr_scene* s, const std::vector<T>& v, const T** dst, 
     s->allocs.push_back(p);
     s->device_bytes += bytes;
     if (!v.empty()) {
-        e = cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+        e = cudaMemcpyAsync((T*)p + prefix, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
         s->h2d_bytes += v.size() * sizeof(T);
     }
     *dst = (const T*)p;
@@ -221,12 +222,22 @@ rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedS
     }
     rtr_scene_desc host_desc = *desc;
     if (out.on_device) { host_desc.objects = nullptr; host_desc.n_objects = 0; }  // materials / background still flatten on the host
+    // Triangle meshes: RTR_BVH_BUILD=device also builds every mesh's BVH on the device (bvh_build.cu build_mesh_on_device).
+    // Not the default: the device builds the reference's median-split topology, the host a SAH tree over the same gates
+    // that needs about half the node visits per ray — a faster upload against a slower render.
+    uint32_t device_mesh_min_tris = 0;
+    {
+        const char* mode = std::getenv("RTR_BVH_BUILD");
+        if (mode && std::strcmp(mode, "device") == 0) device_mesh_min_tris = 2;
+        if (const char* e = std::getenv("RTR_BVH_DEVICE_MESH_MIN_TRIS")) device_mesh_min_tris = (uint32_t)std::max(0, std::atoi(e));
+        if (mode && std::strcmp(mode, "host") == 0) device_mesh_min_tris = 0;
+    }
     for (int attempt = 0; attempt < 2; ++attempt) {
         out.flat = HostFlat();
         std::string err;
         int rc = RTR_OK;
         try {
-            rc = flatten_scene(host_desc, out.flat, err, attempt == 0 ? 8u : 0u);
+            rc = flatten_scene(host_desc, out.flat, err, attempt == 0 ? 8u : 0u, device_mesh_min_tris);
         } catch (const std::bad_alloc&) {
             return fail(ctx, RTR_OOM, "host allocation failed while flattening");
         }
@@ -236,7 +247,7 @@ rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedS
         if (attempt == 1) return fail(ctx, RTR_UNSUPPORTED, "BVH too deep for the traversal stack even when balanced");
     }
     // the 4-wide tree pushes up to three siblings per level; a scene whose worst case would not fit keeps the 2-wide walk
-    if (3u * out.flat.max_depth4 + 4u > stack_limit()) { out.flat.nodes4.clear(); out.flat.root_entry4 = 0xFFFFFFFFu; }
+    if (3u * out.flat.max_depth4 + 4u > stack_limit()) { out.flat.nodes4.clear(); out.flat.device_nodes4 = 0; out.flat.root_entry4 = 0xFFFFFFFFu; }
     out.host_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return RTR_OK;
 }
@@ -250,18 +261,29 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     rtr_scene* s = new (std::nothrow) rtr_scene();
     if (!s) return fail(ctx, RTR_OOM, "host allocation failed");
     s->ctx = ctx;
-    s->n_nodes = (uint32_t)(flat.nodes.size() / 4);
+    s->n_nodes = flat.device_nodes + (uint32_t)(flat.nodes.size() / 4);
     s->max_depth = flat.max_depth;
     SceneView& v = s->view;
     std::memset(&v, 0, sizeof(v));
     cudaError_t e = cudaSuccess;
     auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; };
-    step(upload(s, flat.nodes, &v.nodes, ctx->stream));
-    if (!flat.nodes4.empty() && ctx->wf_wide4) step(upload(s, flat.nodes4, &v.nodes4, ctx->stream));
+    // device-built meshes own the front of the node and triangle arrays (host_flatten.h DeviceMesh); host records follow
+    const bool wide4 = ctx->wf_wide4 != 0u && flat.nodes4.size() + flat.device_nodes4 > 0;
+    step(upload(s, flat.nodes, &v.nodes, ctx->stream, (size_t)flat.device_nodes * 4));
+    if (wide4) step(upload(s, flat.nodes4, &v.nodes4, ctx->stream, (size_t)flat.device_nodes4 * 8));
     step(upload(s, flat.spheres, &v.spheres, ctx->stream));
     step(upload(s, flat.sphere_info, &v.sphere_info, ctx->stream));
-    step(upload(s, flat.tris, &v.tris, ctx->stream));
-    step(upload(s, flat.tri_vn, &v.tri_vn, ctx->stream));
+    step(upload(s, flat.tris, &v.tris, ctx->stream, (size_t)flat.device_tri_slots * 4));
+    step(upload(s, flat.tri_vn, &v.tri_vn, ctx->stream, (size_t)flat.device_tri_slots * 3));
+    for (const DeviceMesh& dm : flat.device_meshes) {
+        if (e != cudaSuccess) break;
+        bool nan_centroid = false, count_mismatch = false;
+        step(build_mesh_on_device(desc->meshes[dm.mesh_index], dm, ctx->stream, ctx->pool, const_cast<F4*>(v.nodes), const_cast<F4*>(v.nodes4),
+                                  const_cast<F4*>(v.tris), const_cast<F4*>(v.tri_vn), &s->h2d_bytes, &nan_centroid, &count_mismatch));
+        if (e == cudaSuccess && nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
+        if (e == cudaSuccess && count_mismatch) { rtr_scene_destroy(s); return fail(ctx, RTR_CUDA_ERROR, "rtr_scene_upload: device mesh build emitted an unexpected number of 4-wide nodes"); }
+        s->built_on_device = true;
+    }
     step(upload(s, flat.volumes, &v.volumes, ctx->stream));
     step(upload(s, flat.objects, &v.objects, ctx->stream));
     step(upload(s, flat.materials, &v.materials, ctx->stream));
@@ -295,9 +317,9 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     v.n_objects = (uint32_t)flat.objects.size();
     v.n_materials = (uint32_t)flat.materials.size();
     v.n_volumes = (uint32_t)flat.volumes.size();
-    v.n_nodes = (uint32_t)(flat.nodes.size() / 4);
+    v.n_nodes = flat.device_nodes + (uint32_t)(flat.nodes.size() / 4);
     v.n_sphere_slots = (uint32_t)flat.spheres.size();
-    v.n_tri_slots = (uint32_t)flat.tri_info.size();
+    v.n_tri_slots = flat.device_tri_slots + (uint32_t)flat.tri_info.size();
     v.linear_needs_inv = 0;
     for (const ObjectRec& o : flat.objects)
         if (RTR_REF_KIND(o.entry) != REF_SPHERE && RTR_REF_KIND(o.entry) != REF_EMPTY) v.linear_needs_inv = 1;

@@ -85,14 +85,15 @@ struct Flattener {
 
     Flattener(HostFlat& o, const rtr_scene_desc& desc, std::string& e) : out(o), d(desc), err(e) {}
 
+    // host-built nodes are numbered after the device-built ones (HostFlat::device_nodes); out.nodes holds only the former
     uint32_t alloc_node() {
         uint32_t idx = (uint32_t)(out.nodes.size() / 4);
         out.nodes.resize(out.nodes.size() + 4, F4{0, 0, 0, 0});
-        return idx;
+        return out.device_nodes + idx;
     }
     static float bits(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
     void write_node_raw(uint32_t idx, uint32_t lref, const Box& lb, uint32_t rref, const Box& rb) {
-        F4* q = &out.nodes[(size_t)idx * 4];
+        F4* q = &out.nodes[(size_t)(idx - out.device_nodes) * 4];
         q[0] = F4{lb.min.x, lb.min.y, lb.min.z, bits(lref)};
         q[1] = F4{lb.max.x, lb.max.y, lb.max.z, bits(rref)};
         q[2] = F4{rb.min.x, rb.min.y, rb.min.z, 0.0f};
@@ -334,21 +335,31 @@ struct Flattener {
     // looked through).  Each slot keeps the box the 2-wide tree tests for it.  Returns the 4-wide ref (a leaf ref as is).
     struct Slot { uint32_t ref; Box box; };
     void slots_of(uint32_t node, std::vector<Slot>& out) const {  // the (at most two) child slots of a 2-wide node
-        const F4* q = &this->out.nodes[(size_t)node * 4];
+        const F4* q = &this->out.nodes[(size_t)(node - this->out.device_nodes) * 4];
         uint32_t l, r;
         std::memcpy(&l, &q[0].w, 4); std::memcpy(&r, &q[1].w, 4);
         if (l != REF_EMPTY_VALUE) out.push_back(Slot{l, Box{V3{q[0].x, q[0].y, q[0].z}, V3{q[1].x, q[1].y, q[1].z}}});
         if (r != REF_EMPTY_VALUE) out.push_back(Slot{r, Box{V3{q[2].x, q[2].y, q[2].z}, V3{q[3].x, q[3].y, q[3].z}}});
     }
+    static uint32_t levels_of(uint32_t n) { uint32_t l = 0; while ((1ull << l) < n) ++l; return l; }
+    const DeviceMesh* device_mesh_at(uint32_t node) const {  // the device-built mesh whose root Split this is
+        for (const DeviceMesh& m : out.device_meshes) if (m.node_base == node) return &m;
+        return nullptr;
+    }
     uint32_t collapse4(uint32_t entry, uint32_t* depth) {
         if (entry == REF_EMPTY_VALUE || RTR_REF_KIND(entry) != REF_NODE) { *depth = entry == REF_EMPTY_VALUE ? 0u : 1u; return entry; }
+        if (RTR_REF_INDEX(entry) < out.device_nodes) {  // the root Split of a device-built mesh: its 4-wide root
+            const DeviceMesh* m = device_mesh_at(RTR_REF_INDEX(entry));
+            *depth = levels_of(m->n_tris) / 2u + 2u;
+            return RTR_MAKE_REF(REF_NODE, m->node4_base);
+        }
         std::vector<Slot> s;
         slots_of(RTR_REF_INDEX(entry), s);
         for (;;) {
             int pick = -1;
             float best = -1.0f;
             for (size_t i = 0; i < s.size(); ++i) {
-                if (RTR_REF_KIND(s[i].ref) != REF_NODE) continue;
+                if (RTR_REF_KIND(s[i].ref) != REF_NODE || RTR_REF_INDEX(s[i].ref) < out.device_nodes) continue;
                 std::vector<Slot> kids;
                 slots_of(RTR_REF_INDEX(s[i].ref), kids);
                 if (kids.size() <= 1) { pick = (int)i; break; }  // a single-child pseudo parent costs no slot: look through it
@@ -362,7 +373,8 @@ struct Flattener {
             s.erase(s.begin() + pick);
             s.insert(s.begin() + pick, kids.begin(), kids.end());
         }
-        const uint32_t idx = (uint32_t)(out.nodes4.size() / 8);
+        const size_t local = out.nodes4.size() / 8;
+        const uint32_t idx = out.device_nodes4 + (uint32_t)local;
         out.nodes4.resize(out.nodes4.size() + 8, F4{0, 0, 0, 0});
         uint32_t refs[4] = {REF_EMPTY_VALUE, REF_EMPTY_VALUE, REF_EMPTY_VALUE, REF_EMPTY_VALUE};
         Box boxes[4] = {};
@@ -373,7 +385,7 @@ struct Flattener {
             boxes[i] = s[i].box;
             deepest = std::max(deepest, d);
         }
-        F4* q = &out.nodes4[(size_t)idx * 8];
+        F4* q = &out.nodes4[local * 8];
         for (int i = 0; i < 4; ++i) {
             q[2 * i] = F4{boxes[i].min.x, boxes[i].min.y, boxes[i].min.z, 0.0f};
             q[2 * i + 1] = F4{boxes[i].max.x, boxes[i].max.y, boxes[i].max.z, 0.0f};
@@ -409,7 +421,7 @@ struct Flattener {
             V3 fn = normalize(cross(sub(p2, p1), sub(p0, p1)));
             // edges as Triangle::hit computes them (mesh.rs:160-161)
             V3 e1 = sub(p1, p0), e2 = sub(p2, p0);
-            uint32_t slot = (uint32_t)f.out.tri_info.size();
+            uint32_t slot = f.out.device_tri_slots + (uint32_t)f.out.tri_info.size();
             f.out.tris.push_back(F4{p0.x, p0.y, p0.z, fn.x});
             f.out.tris.push_back(F4{e1.x, e1.y, e1.z, fn.y});
             f.out.tris.push_back(F4{e2.x, e2.y, e2.z, fn.z});
@@ -430,6 +442,17 @@ struct Flattener {
 
     Built emit_mesh(uint32_t mesh_index, uint32_t object) {
         const rtr_mesh& m = d.meshes[mesh_index];
+        for (DeviceMesh& dm : out.device_meshes) {
+            if (dm.object != object) continue;
+            // Built on the device: reserve the DFS ranks of its triangles and hand the enclosing collection the root
+            // Split (node_base; both walks share the device-built nodes) with the box from_list gives it (bvh.rs:68-72).
+            dm.rank_base = rank;
+            rank += dm.n_tris;
+            MeshColl coll(*this, m, object);
+            Box root = coll.bounds(0);
+            for (uint32_t h = 1; h < dm.n_tris; ++h) root = surround(root, coll.bounds(h));
+            return Built(RTR_MAKE_REF(REF_NODE, dm.node_base), root, true, levels_of(dm.n_tris) + 1u);
+        }
         MeshColl coll(*this, m, object);
         std::vector<uint32_t> handles(m.n_indices / 3);
         for (size_t i = 0; i < handles.size(); ++i) handles[i] = (uint32_t)i;
@@ -553,8 +576,45 @@ bool validate(const rtr_scene_desc& d, std::string& err) {
 
 }  // namespace
 
-int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint32_t slack) {
+uint32_t count_nodes4(uint32_t n) {
+    // bvh_build.cu k_flag4: the Splits at even depth holding three or more leaves, plus the root.  A median-split subtree
+    // is determined by its size, and one level holds at most two distinct sizes: walk the levels with (size, count) pairs.
+    if (n < 2) return 0;
+    uint64_t total = 0;
+    std::vector<std::pair<uint32_t, uint64_t>> level{{n, 1}}, next;
+    for (uint32_t depth = 0; !level.empty(); ++depth) {
+        next.clear();
+        for (const auto& sc : level) {
+            if (sc.first < 2) continue;
+            if ((depth & 1u) == 0u && (sc.first >= 3 || depth == 0)) total += sc.second;
+            const uint32_t parts[2] = {sc.first / 2, sc.first - sc.first / 2};
+            for (uint32_t part : parts) {
+                bool merged = false;
+                for (auto& e : next) if (e.first == part) { e.second += sc.second; merged = true; break; }
+                if (!merged) next.push_back({part, sc.second});
+            }
+        }
+        level.swap(next);
+    }
+    return (uint32_t)total;
+}
+
+int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint32_t slack, uint32_t device_mesh_min_tris) {
     if (!validate(d, err)) return err.find("unsupported") != std::string::npos ? RTR_UNSUPPORTED : RTR_INVALID_ARG;
+    if (device_mesh_min_tris) {
+        // every object that is a mesh, or a Volume bounded directly by one, and is big enough: its index ranges
+        for (uint32_t i = 0; i < d.n_objects; ++i) {
+            rtr_object_ref r = d.objects[i];
+            if (r.kind == RTR_OBJ_VOLUME) r = d.volumes[r.index].boundary;  // a Volume bounded by a Volume emits no boundary
+            if (r.kind != RTR_OBJ_MESH) continue;
+            const rtr_mesh& m = d.meshes[r.index];
+            const uint32_t n = m.n_indices / 3;
+            if (n < 2 || n < device_mesh_min_tris) continue;
+            DeviceMesh dm{r.index, i, m.material, n, out.device_tri_slots, out.device_nodes, out.device_nodes4, 0u};
+            out.device_tri_slots += n; out.device_nodes += n; out.device_nodes4 += count_nodes4(n);
+            out.device_meshes.push_back(dm);
+        }
+    }
     Flattener f(out, d, err);
     f.slack = slack;
     out.nodes.reserve(64);

@@ -10,7 +10,21 @@
 
 namespace rtr {
 
+// A mesh whose BVH is built on the device (bvh_build.cu) instead of by the host flattener.  The host only reserves its
+// index ranges — device-built records occupy the FRONT of the device arrays, the host-built ones follow — and refers
+// to it through its root Split, node_base (4-wide tree: node4_base).
+struct DeviceMesh {
+    uint32_t mesh_index, object, material, n_tris;
+    uint32_t slot_base;    // first triangle slot (tris / tri_vn)
+    uint32_t node_base;    // first 2-wide node; the mesh owns n_tris of them
+    uint32_t node4_base;   // first 4-wide node; the mesh owns count_nodes4(n_tris)
+    uint32_t rank_base;    // DFS leaf rank of its first triangle (bvh.rs:183-187 tie rule)
+};
+uint32_t count_nodes4(uint32_t n_leaves);  // 4-wide nodes the device collapse emits for a median-split tree of n leaves
+
 struct HostFlat {
+    std::vector<DeviceMesh> device_meshes;
+    uint32_t device_nodes = 0, device_nodes4 = 0, device_tri_slots = 0;  // sizes of the device-built prefixes; host indices start there
     std::vector<F4> nodes, spheres, tris, tri_vn, env;
     std::vector<F4> nodes4;                       // 4-wide traversal tree (flat.h), 8 per node; empty when not built
     uint32_t root_entry4 = 0xFFFFFFFFu;
@@ -28,7 +42,8 @@ struct HostFlat {
 
 // returns an rtr_status; on failure `err` says why.  `slack` = levels a collection's SAH traversal tree may exceed its
 // balanced depth ceil(log2 n) by (0: every split is the median, the minimal depth)
-int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err, uint32_t slack = 8);
+// `device_mesh_min_tris`: meshes with at least this many triangles are left to the device builder (0 = none)
+int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err, uint32_t slack = 8, uint32_t device_mesh_min_tris = 0);
 
 }  // namespace rtr
 #endif
