@@ -443,7 +443,7 @@ class Bench:
                 "algorithmic_bytes_per_launch": alg, "bytes_per_ray": alg / max(rays_rank, 1),
                 "traversed": {"bytes_per_launch": alg_trav, "bytes_per_ray": alg_trav / max(rays_rank, 1),
                               "achieved": alg_trav / (k_ms * 1e-3) / 1e9, "frac": alg_trav / (k_ms * 1e-3) / 1e9 / self.peak,
-                              "note": "the same formula counted on the traversal tree the timed kernel actually walks (binned SAH over the gate boxes, paired leaves)"},
+                              "note": "the same formula counted on the tree the timed kernel actually walks (binned SAH over the gate boxes, paired leaves; the wavefront walks its 4-wide collapse, nodes_visited = boxes tested)"},
                 "traffic": traffic_launch,
                 "traffic_note": "dram__bytes_read+write summed over every launch of a wave (ncu --set full), per ray x this step's rays; "
                                 "far below the algorithmic bytes because the scene is L2/L1-resident",

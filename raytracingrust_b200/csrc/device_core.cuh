@@ -349,13 +349,14 @@ __device__ __forceinline__ void order2(float& ea, uint32_t& ra, float& eb, uint3
     const uint32_t r0 = sw ? rb : ra, r1 = sw ? ra : rb;
     ea = e0; eb = e1; ra = r0; rb = r1;
 }
-template <typename STACK>
+template <bool COUNT, typename STACK>
 __device__ __forceinline__ void node4_step(const SceneView& sc, uint32_t& cur, int& sp, const LiteHit& best, const Ray& r,
-                                           const RayInv& inv, float tmin, float tmax, const STACK& stack, int floor = 0) {
+                                           const RayInv& inv, float tmin, float tmax, const STACK& stack, Counters* cnt, int floor = 0) {
     const F4* q = sc.nodes4 + (size_t)RTR_REF_INDEX(cur) * 8;
     float4 q0, q1, q2, q3, q4, q5, q6, q7;
     ldg8(q, q0, q1); ldg8(q + 2, q2, q3); ldg8(q + 4, q4, q5); ldg8(q + 6, q6, q7);
     uint32_t r0 = __float_as_uint(q0.w), r1 = __float_as_uint(q1.w), r2 = __float_as_uint(q2.w), r3 = __float_as_uint(q3.w);
+    if (COUNT) cnt->nodes += (r0 != REF_EMPTY_VALUE) + (r1 != REF_EMPTY_VALUE) + (r2 != REF_EMPTY_VALUE) + (r3 != REF_EMPTY_VALUE);  // boxes tested
     const float lim = cull_limit(best.t);
     float e0, e1, e2, e3;
     const bool h0 = slab(q0, q1, r, inv, tmin, tmax, e0) && r0 != REF_EMPTY_VALUE && !(e0 > lim);

@@ -37,13 +37,14 @@ enum : uint32_t {
 #define RTR_MAKE_REF(kind, idx) (((uint32_t)(kind) << 29) | (uint32_t)(idx))
 static const uint32_t REF_EMPTY_VALUE = 0xFFFFFFFFu;  // kind 7
 
-// 4-wide traversal node (128 B, 128-B aligned, 8 x float4), host-built scenes only: the SAH traversal tree with every
-// other level folded away.  Child k's box is the SAME box its slot carries in the 2-wide tree (an interior box is a
-// union of gates, a leaf slot carries its gate), so the candidate set — every leaf whose gate is pierced — is unchanged:
+// 4-wide traversal node (128 B, 128-B aligned, 8 x float4): the traversal tree with every other level folded away
+// (host_flatten.cpp collapse4 for host-built trees, bvh_build.cu k_emit_nodes4 for device-built ones).  Child k's box
+// is the SAME box its slot carries in the 2-wide tree (an interior box is a union of gates, a leaf slot carries its
+// gate), so the candidate set — every leaf whose gate is pierced — is unchanged:
 //   q0 = { c0.min, bits(ref0) }  q1 = { c0.max, bits(ref1) }  q2 = { c1.min, bits(ref2) }  q3 = { c1.max, bits(ref3) }
 //   q4 = { c2.min, 0 }           q5 = { c2.max, 0 }           q6 = { c3.min, 0 }           q7 = { c3.max, 0 }
-// REF_NODE references inside nodes4 index nodes4; unused slots hold REF_EMPTY.  Only the 4-wide instantiation of wf_extend
-// walks it (SceneView::root_entry4, VolumeRec::entry4, ObjectRec::entry4); every other walk uses the 2-wide arrays.
+// REF_NODE references inside nodes4 index nodes4; unused slots hold REF_EMPTY.  Only the 4-wide instantiations of
+// wf_extend walk it (SceneView::root_entry4, VolumeRec::entry4, ObjectRec::entry4); every other walk uses the 2-wide arrays.
 struct F4 { float x, y, z, w; };
 struct U4 { uint32_t x, y, z, w; };
 
@@ -89,7 +90,7 @@ struct BackgroundRec {
 // Device view: raw pointers into one allocation each.
 struct SceneView {
     const F4* nodes;          // 4 per node
-    const F4* nodes4;         // 8 per 4-wide node (null: the scene has no 4-wide tree, e.g. it was built on the device)
+    const F4* nodes4;         // 8 per 4-wide node (null: no 4-wide tree — RTR_WF_WIDE=0, or its stack need exceeds the limit)
     uint32_t root_entry4;     // entry ref of the 4-wide traversal tree
     uint32_t _pad4;
     const F4* spheres;        // (cx, cy, cz, r) per slot

@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(256) wf_bin_kernel(const WfArgs a) {
 // and the per-ray RNG key from the traversal state (ncu: local-memory traffic was 44 % of wf_extend's L1 wavefronts).
 // TMIN_ARG = true: world.hit's tmin comes from the arguments (rtr_trace_batch with a tmin other than render()'s 1e-5);
 // the render path keeps the literal, which costs the volume instantiation 30 bytes of spills less.
-// WIDE4 = true: interior steps walk the 4-wide tree (flat.h: nodes4, node4_step); culled, non-counting, render-tmin walks only.
+// WIDE4 = true: interior steps walk the 4-wide tree (flat.h: nodes4, node4_step); culled, render-tmin walks of the traversal tree only.
 template <bool EXHAUSTIVE, bool COUNT, bool VOLUMES, bool TMIN_ARG = false, bool WIDE4 = false>
 __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, WIDE4 ? (VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS_W4 : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4)
                                                                : (VOLUMES ? RTR_WF_EXTEND_MIN_BLOCKS : RTR_WF_EXTEND_MIN_BLOCKS_NOVOL)) wf_extend_kernel(const WfArgs a) {
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(RTR_WF_EXTEND_THREADS, WIDE4 ? (VOLUMES ? RTR_
                     const uint32_t ml = __ballot_sync(FULL, !at_node && cur != RTR_REF_DONE);
                     if (mn == 0u || __popc(mn) < __popc(ml)) break;
                     if (at_node && WIDE4) {
-                        node4_step(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, VOLUMES ? floor : 0);
+                        node4_step<COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
                     } else if (at_node) {
                         node_step<EXHAUSTIVE, COUNT>(a.sc, cur, sp, best, r, inv, VOLUMES ? tmin_cur : tmin0, RTR_INF, wstack, &cnt, VOLUMES ? floor : 0);
 #if RTR_WF_NODE_BURST
@@ -530,7 +530,8 @@ cudaError_t launch_trace_finish(const WfArgs& a, uint32_t n, rtr_hit* out, cudaS
 // ------------------------------------------------------------------ launchers
 template <typename F>
 static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_arg, bool wide4, F f) {
-    if (wide4 && !exhaustive && !count && !tmin_arg) {
+    if (wide4 && !exhaustive && !tmin_arg) {
+        if (count) { if (volumes) return f(wf_extend_kernel<false, true, true, false, true>); return f(wf_extend_kernel<false, true, false, false, true>); }
         if (volumes) return f(wf_extend_kernel<false, false, true, false, true>);
         return f(wf_extend_kernel<false, false, false, false, true>);
     }
@@ -546,7 +547,8 @@ static auto pick_wf_extend(bool exhaustive, bool count, bool volumes, bool tmin_
 }
 
 bool wf_extend_wide4(const WfArgs& a, bool exhaustive, bool count) {
-    return a.sc.nodes4 != nullptr && a.sc.reference_tree == 0u && a.enable_bvh_tree != 0u && !exhaustive && !count && a.tmin == 0.00001f;
+    (void)count;  // the counting instantiations walk it too (nodes_visited = boxes tested), unless they walk the reference topology
+    return a.sc.nodes4 != nullptr && a.sc.reference_tree == 0u && a.enable_bvh_tree != 0u && !exhaustive && a.tmin == 0.00001f;
 }
 
 int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool tmin_arg, bool wide4) {
