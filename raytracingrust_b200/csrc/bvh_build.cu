@@ -259,6 +259,29 @@ __global__ void k_emit_nodes(BuildArrays a, F4* nodes) {
     }
 }
 
+// Gated entries for a host-built traversal tree (hybrid build, host_flatten.h build_traversal_over_gates): per leaf
+// position {gate.min, bits(ref)} {gate.max, 0} — a single leaf is gated by its parent's box, the two leaves of a 2-leaf
+// Split are ONE paired entry gated by that Split's own box (the second position holds EMPTY).
+__global__ void k_emit_gated(BuildArrays a, F4* gated) {
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node + 1u >= a.n) return;
+    const uint32_t lo = a.node_lo[node], hi = a.node_hi[node], mid = lo + (hi - lo) / 2u;
+    if (hi - lo < 3u) return;  // a 2-leaf Split is written by its parent
+    const uint32_t clo[2] = {lo, mid}, chi[2] = {mid, hi}, cnode[2] = {node + 1u, node + (mid - lo)};
+    for (int k = 0; k < 2; ++k) {
+        const uint32_t n = chi[k] - clo[k];
+        if (n > 2u) continue;
+        float4 mn, mx;
+        const uint32_t ref = child_ref(a, clo[k], chi[k], cnode[k], node, mn, mx);
+        gated[2 * (size_t)clo[k]] = F4{mn.x, mn.y, mn.z, __uint_as_float(ref)};
+        gated[2 * (size_t)clo[k] + 1] = F4{mx.x, mx.y, mx.z, 0.0f};
+        if (n == 2u) {
+            gated[2 * (size_t)clo[k] + 2] = F4{0.0f, 0.0f, 0.0f, __uint_as_float(REF_EMPTY_VALUE)};
+            gated[2 * (size_t)clo[k] + 3] = F4{0.0f, 0.0f, 0.0f, 0.0f};
+        }
+    }
+}
+
 // ---- 4-wide traversal tree (flat.h nodes4) ----------------------------------------------------------------------
 // The tree's shape depends on n alone and every interior child of a Split can be replaced by its own two children
 // without overflowing four slots, so the 4-wide nodes are exactly the Splits at even depth that hold three or more
@@ -475,7 +498,7 @@ cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t s
 }
 
 cudaError_t build_mesh_on_device(const rtr_mesh& mesh, const DeviceMesh& dm, cudaStream_t st, cudaMemPool_t pool, F4* nodes, F4* nodes4,
-                                 F4* tris, F4* tri_vn, uint64_t* h2d_bytes, bool* nan_centroid, bool* count_mismatch) {
+                                 F4* tris, F4* tri_vn, uint64_t* h2d_bytes, bool* nan_centroid, bool* count_mismatch, std::vector<F4>* gated_out) {
     const uint32_t n = dm.n_tris;
     Builder b;
     b.st = st; b.pool = pool;
@@ -499,6 +522,13 @@ cudaError_t build_mesh_on_device(const rtr_mesh& mesh, const DeviceMesh& dm, cud
     k_emit_leaves_tri<<<b.grid, 256, 0, st>>>(a, in, tris, tri_vn);
     b.emit_nodes(nodes);
     if (nodes4) { b.number_nodes4(); b.emit_nodes4(nodes4); }  // the host reserved count_nodes4(n) records (host_flatten.h)
+    if (gated_out) {  // hybrid: the gates go back to the host, which builds the SAH traversal tree over them
+        F4* d_gated = (F4*)b.alloc((size_t)n * 2 * sizeof(F4));
+        gated_out->resize((size_t)n * 2);
+        if (b.e == cudaSuccess) k_emit_gated<<<b.grid, 256, 0, st>>>(a, d_gated);
+        b.step(cudaGetLastError());
+        b.step(cudaMemcpyAsync(gated_out->data(), d_gated, (size_t)n * 2 * sizeof(F4), cudaMemcpyDeviceToHost, st));
+    }
     uint32_t h_flags[4] = {0, 0, 0, 0};
     uint32_t h_last[2] = {0, 0};
     b.step(cudaMemcpyAsync(h_flags, a.flags, 16, cudaMemcpyDeviceToHost, st));

@@ -38,7 +38,8 @@ cudaError_t build_sphere_scene_on_device(const rtr_scene_desc& d, cudaStream_t s
 // triangle records into the ranges `dm` reserves in the scene's device arrays.  Scratch and the device copies of the vertex
 // buffers come from `pool` and are freed before returning.  Synchronises `st`.
 cudaError_t build_mesh_on_device(const rtr_mesh& mesh, const DeviceMesh& dm, cudaStream_t st, cudaMemPool_t pool, F4* nodes, F4* nodes4,
-                                 F4* tris, F4* tri_vn, uint64_t* h2d_bytes, bool* nan_centroid, bool* count_mismatch);
+                                 F4* tris, F4* tri_vn, uint64_t* h2d_bytes, bool* nan_centroid, bool* count_mismatch,
+                                 std::vector<F4>* gated_out = nullptr);  // hybrid: the gated entries (host_flatten.h), after the sync
 
 }  // namespace rtr
 #endif

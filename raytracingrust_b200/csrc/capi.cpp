@@ -225,10 +225,15 @@ rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedS
     // Triangle meshes: RTR_BVH_BUILD=device also builds every mesh's BVH on the device (bvh_build.cu build_mesh_on_device).
     // Not the default: the device builds the reference's median-split topology, the host a SAH tree over the same gates
     // that needs about half the node visits per ray — a faster upload against a slower render.
+    // RTR_BVH_BUILD=hybrid: the device builds each mesh's reference tree (the O(n log^2 n) sorts, gates, ranks, records) and
+    // the host builds the SAH traversal tree over the gates it reads back — the device's upload speed for the sorts, the
+    // host tree's render speed.
     uint32_t device_mesh_min_tris = 0;
+    bool hybrid = false;
     {
         const char* mode = std::getenv("RTR_BVH_BUILD");
         if (mode && std::strcmp(mode, "device") == 0) device_mesh_min_tris = 2;
+        if (mode && std::strcmp(mode, "hybrid") == 0) { device_mesh_min_tris = 3; hybrid = true; }
         if (const char* e = std::getenv("RTR_BVH_DEVICE_MESH_MIN_TRIS")) device_mesh_min_tris = (uint32_t)std::max(0, std::atoi(e));
         if (mode && std::strcmp(mode, "host") == 0) device_mesh_min_tris = 0;
     }
@@ -237,7 +242,7 @@ rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedS
         std::string err;
         int rc = RTR_OK;
         try {
-            rc = flatten_scene(host_desc, out.flat, err, attempt == 0 ? 8u : 0u, device_mesh_min_tris);
+            rc = flatten_scene(host_desc, out.flat, err, attempt == 0 ? 8u : 0u, device_mesh_min_tris, hybrid);
         } catch (const std::bad_alloc&) {
             return fail(ctx, RTR_OOM, "host allocation failed while flattening");
         }
@@ -275,15 +280,38 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     step(upload(s, flat.sphere_info, &v.sphere_info, ctx->stream));
     step(upload(s, flat.tris, &v.tris, ctx->stream, (size_t)flat.device_tri_slots * 4));
     step(upload(s, flat.tri_vn, &v.tri_vn, ctx->stream, (size_t)flat.device_tri_slots * 3));
+    bool wide4_ok = true;
     for (const DeviceMesh& dm : flat.device_meshes) {
         if (e != cudaSuccess) break;
         bool nan_centroid = false, count_mismatch = false;
-        step(build_mesh_on_device(desc->meshes[dm.mesh_index], dm, ctx->stream, ctx->pool, const_cast<F4*>(v.nodes), const_cast<F4*>(v.nodes4),
-                                  const_cast<F4*>(v.tris), const_cast<F4*>(v.tri_vn), &s->h2d_bytes, &nan_centroid, &count_mismatch));
+        std::vector<F4> gated;
+        step(build_mesh_on_device(desc->meshes[dm.mesh_index], dm, ctx->stream, ctx->pool, const_cast<F4*>(v.nodes),
+                                  dm.hybrid ? nullptr : const_cast<F4*>(v.nodes4), const_cast<F4*>(v.tris), const_cast<F4*>(v.tri_vn),
+                                  &s->h2d_bytes, &nan_centroid, &count_mismatch, dm.hybrid ? &gated : nullptr));
         if (e == cudaSuccess && nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
         if (e == cudaSuccess && count_mismatch) { rtr_scene_destroy(s); return fail(ctx, RTR_CUDA_ERROR, "rtr_scene_upload: device mesh build emitted an unexpected number of 4-wide nodes"); }
+        if (e == cudaSuccess && dm.hybrid) {  // the host's SAH tree over the device-built gates, into the ranges reserved for it
+            std::vector<F4> sah, sah4;
+            uint32_t depth = 0, depth4 = 0;
+            try {
+                build_traversal_over_gates(gated.data(), dm.n_tris, dm.sah_base, dm.node4_base, dm.slack, sah, sah4, &depth, &depth4);
+            } catch (const std::bad_alloc&) {
+                rtr_scene_destroy(s);
+                return fail(ctx, RTR_OOM, "host allocation failed while building the traversal tree");
+            }
+            if (sah.size() / 4 != (size_t)dm.n_gated - 1u || sah4.size() / 8 > (size_t)dm.n_gated - 1u) {
+                rtr_scene_destroy(s);
+                return fail(ctx, RTR_CUDA_ERROR, "rtr_scene_upload: the device-built gates do not match the reserved traversal-tree size");
+            }
+            if (depth4 > dm.depth4_estimate) wide4_ok = false;  // deeper than the stack check assumed: this scene keeps the 2-wide walk
+            step(cudaMemcpyAsync(const_cast<F4*>(v.nodes) + (size_t)dm.sah_base * 4, sah.data(), sah.size() * sizeof(F4), cudaMemcpyHostToDevice, ctx->stream));
+            if (v.nodes4) step(cudaMemcpyAsync(const_cast<F4*>(v.nodes4) + (size_t)dm.node4_base * 8, sah4.data(), sah4.size() * sizeof(F4), cudaMemcpyHostToDevice, ctx->stream));
+            step(cudaStreamSynchronize(ctx->stream));  // sah / sah4 die here
+            s->h2d_bytes += (sah.size() + sah4.size()) * sizeof(F4);
+        }
         s->built_on_device = true;
     }
+    if (!wide4_ok) v.nodes4 = nullptr;
     step(upload(s, flat.volumes, &v.volumes, ctx->stream));
     step(upload(s, flat.objects, &v.objects, ctx->stream));
     step(upload(s, flat.materials, &v.materials, ctx->stream));

@@ -343,14 +343,14 @@ struct Flattener {
     }
     static uint32_t levels_of(uint32_t n) { uint32_t l = 0; while ((1ull << l) < n) ++l; return l; }
     const DeviceMesh* device_mesh_at(uint32_t node) const {  // the device-built mesh whose root Split this is
-        for (const DeviceMesh& m : out.device_meshes) if (m.node_base == node) return &m;
+        for (const DeviceMesh& m : out.device_meshes) if (m.node_base == node || (m.hybrid && m.sah_base == node)) return &m;
         return nullptr;
     }
     uint32_t collapse4(uint32_t entry, uint32_t* depth) {
         if (entry == REF_EMPTY_VALUE || RTR_REF_KIND(entry) != REF_NODE) { *depth = entry == REF_EMPTY_VALUE ? 0u : 1u; return entry; }
         if (RTR_REF_INDEX(entry) < out.device_nodes) {  // the root Split of a device-built mesh: its 4-wide root
             const DeviceMesh* m = device_mesh_at(RTR_REF_INDEX(entry));
-            *depth = levels_of(m->n_tris) / 2u + 2u;
+            *depth = m->hybrid ? m->depth4_estimate : levels_of(m->n_tris) / 2u + 2u;
             return RTR_MAKE_REF(REF_NODE, m->node4_base);
         }
         std::vector<Slot> s;
@@ -451,7 +451,9 @@ struct Flattener {
             MeshColl coll(*this, m, object);
             Box root = coll.bounds(0);
             for (uint32_t h = 1; h < dm.n_tris; ++h) root = surround(root, coll.bounds(h));
-            return Built(RTR_MAKE_REF(REF_NODE, dm.node_base), root, true, levels_of(dm.n_tris) + 1u);
+            Built b(RTR_MAKE_REF(REF_NODE, dm.node_base), root, true, levels_of(dm.n_tris) + 1u);
+            if (dm.hybrid) { b.fast_ref = RTR_MAKE_REF(REF_NODE, dm.sah_base); b.fast_depth = levels_of(dm.n_tris) + dm.slack; }  // upper bound
+            return b;
         }
         MeshColl coll(*this, m, object);
         std::vector<uint32_t> handles(m.n_indices / 3);
@@ -599,7 +601,54 @@ uint32_t count_nodes4(uint32_t n) {
     return (uint32_t)total;
 }
 
-int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint32_t slack, uint32_t device_mesh_min_tris) {
+uint32_t count_gated(uint32_t n) {
+    if (n == 0) return 0;
+    uint64_t total = 0;
+    std::vector<std::pair<uint32_t, uint64_t>> level{{n, 1}}, next;
+    while (!level.empty()) {
+        next.clear();
+        for (const auto& sc : level) {
+            if (sc.first <= 2) { total += sc.second; continue; }  // a single leaf, or a 2-leaf Split folded into one paired leaf
+            const uint32_t parts[2] = {sc.first / 2, sc.first - sc.first / 2};
+            for (uint32_t part : parts) {
+                bool merged = false;
+                for (auto& e : next) if (e.first == part) { e.second += sc.second; merged = true; break; }
+                if (!merged) next.push_back({part, sc.second});
+            }
+        }
+        level.swap(next);
+    }
+    return (uint32_t)total;
+}
+
+void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t node_base, uint32_t node4_base, uint32_t slack,
+                                std::vector<F4>& nodes, std::vector<F4>& nodes4, uint32_t* depth, uint32_t* depth4) {
+    HostFlat tmp;
+    tmp.device_nodes = node_base; tmp.device_nodes4 = node4_base;  // the Flattener numbers its nodes from these
+    rtr_scene_desc none;
+    std::memset(&none, 0, sizeof(none));
+    std::string err;
+    Flattener f(tmp, none, err);
+    f.slack = slack;
+    std::vector<GatedLeaf> L;
+    L.reserve(n_positions);
+    for (uint32_t p = 0; p < n_positions; ++p) {
+        uint32_t ref;
+        std::memcpy(&ref, &gated[2 * (size_t)p].w, 4);
+        if (ref == REF_EMPTY_VALUE) continue;
+        const F4& mn = gated[2 * (size_t)p]; const F4& mx = gated[2 * (size_t)p + 1];
+        L.push_back(GatedLeaf{ref, Box{V3{mn.x, mn.y, mn.z}, V3{mx.x, mx.y, mx.z}}, 1u});
+    }
+    uint32_t levels = 0;
+    while ((size_t(1) << levels) < n_positions) ++levels;
+    const Flattener::FastOut o = f.build_traversal(L, 0, L.size(), levels + slack);  // as build_collection does for a host-built mesh
+    uint32_t d4 = 0;
+    f.collapse4(o.ref, &d4);
+    nodes.swap(tmp.nodes); nodes4.swap(tmp.nodes4);
+    *depth = o.depth; *depth4 = d4;
+}
+
+int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint32_t slack, uint32_t device_mesh_min_tris, bool hybrid) {
     if (!validate(d, err)) return err.find("unsupported") != std::string::npos ? RTR_UNSUPPORTED : RTR_INVALID_ARG;
     if (device_mesh_min_tris) {
         // every object that is a mesh, or a Volume bounded directly by one, and is big enough: its index ranges
@@ -609,9 +658,21 @@ int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint
             if (r.kind != RTR_OBJ_MESH) continue;
             const rtr_mesh& m = d.meshes[r.index];
             const uint32_t n = m.n_indices / 3;
-            if (n < 2 || n < device_mesh_min_tris) continue;
-            DeviceMesh dm{r.index, i, m.material, n, out.device_tri_slots, out.device_nodes, out.device_nodes4, 0u};
-            out.device_tri_slots += n; out.device_nodes += n; out.device_nodes4 += count_nodes4(n);
+            if (n < (hybrid ? 3u : 2u) || n < device_mesh_min_tris) continue;
+            DeviceMesh dm{r.index, i, m.material, n, out.device_tri_slots, out.device_nodes, out.device_nodes4, 0u, 0u, 0u, 0u, slack, 0u};
+            out.device_tri_slots += n; out.device_nodes += n;
+            if (hybrid) {
+                dm.hybrid = 1u;
+                dm.n_gated = count_gated(n);
+                dm.sah_base = out.device_nodes;
+                out.device_nodes += dm.n_gated - 1u;    // a binary tree over n_gated entries
+                out.device_nodes4 += dm.n_gated - 1u;   // its 4-wide collapse has at most as many nodes
+                uint32_t levels = 0;
+                while ((1ull << levels) < n) ++levels;
+                dm.depth4_estimate = (levels + slack) / 2u + 2u;  // checked against the tree actually built at upload time
+            } else {
+                out.device_nodes4 += count_nodes4(n);
+            }
             out.device_meshes.push_back(dm);
         }
     }

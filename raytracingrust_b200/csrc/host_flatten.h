@@ -19,8 +19,16 @@ struct DeviceMesh {
     uint32_t node_base;    // first 2-wide node; the mesh owns n_tris of them
     uint32_t node4_base;   // first 4-wide node; the mesh owns count_nodes4(n_tris)
     uint32_t rank_base;    // DFS leaf rank of its first triangle (bvh.rs:183-187 tie rule)
+    // hybrid: the device builds the reference tree (gates, ranks, records), the host then builds the SAH traversal tree over
+    // the gates it reads back (build_traversal_over_gates): n_gated - 1 nodes from sah_base, its 4-wide collapse from node4_base
+    uint32_t hybrid, sah_base, n_gated, slack, depth4_estimate;
 };
 uint32_t count_nodes4(uint32_t n_leaves);  // 4-wide nodes the device collapse emits for a median-split tree of n leaves
+uint32_t count_gated(uint32_t n_leaves);   // gated entries of that tree: single leaves + 2-leaf Splits (paired leaves)
+// SAH traversal tree + its 4-wide collapse over gated entries read back from the device (2 x F4 per leaf position:
+// {gate.min, bits(ref)} {gate.max, 0}; ref EMPTY = the second leaf of a pair).  Node indices start at node_base / node4_base.
+void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t node_base, uint32_t node4_base, uint32_t slack,
+                                std::vector<F4>& nodes, std::vector<F4>& nodes4, uint32_t* depth, uint32_t* depth4);
 
 struct HostFlat {
     std::vector<DeviceMesh> device_meshes;
@@ -42,8 +50,10 @@ struct HostFlat {
 
 // returns an rtr_status; on failure `err` says why.  `slack` = levels a collection's SAH traversal tree may exceed its
 // balanced depth ceil(log2 n) by (0: every split is the median, the minimal depth)
-// `device_mesh_min_tris`: meshes with at least this many triangles are left to the device builder (0 = none)
-int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err, uint32_t slack = 8, uint32_t device_mesh_min_tris = 0);
+// `device_mesh_min_tris`: meshes with at least this many triangles are left to the device builder (0 = none);
+// `hybrid`: ... and get a host-built SAH traversal tree over the device-built gates at upload time
+int flatten_scene(const rtr_scene_desc& desc, HostFlat& out, std::string& err, uint32_t slack = 8, uint32_t device_mesh_min_tris = 0,
+                  bool hybrid = false);
 
 }  // namespace rtr
 #endif

@@ -132,12 +132,16 @@ MESH_SCENES = {"mesh_hdri": lambda: _scenes.mesh_hdri(64, 32), "volumes": lambda
                "mixed": meshes_spheres_and_media}
 
 
+@pytest.mark.parametrize("mode", ["device", "hybrid"])
 @pytest.mark.parametrize("name", sorted(MESH_SCENES))
-def test_device_mesh_build_equals_host_build_and_oracle(ctx, name):
+def test_device_mesh_build_equals_host_build_and_oracle(ctx, name, mode):
+    """device: reference tree, records and traversal all from the device; hybrid: the host adds its SAH traversal tree over
+    the gates the device built (RTR_BVH_BUILD, capi.cpp prepare_scene)."""
     scene = MESH_SCENES[name]()
     rays = np.concatenate([_scenes.camera_rays_np(scene, 128, 96), _scenes.random_rays(20000, 3, 3.0)])
-    dev, host = upload(ctx, scene, "device"), upload(ctx, scene, "host")
-    assert dev.info()["n_nodes"] < host.info()["n_nodes"]  # one shared tree per mesh instead of reference + traversal tree
+    dev, host = upload(ctx, scene, mode), upload(ctx, scene, "host")
+    if mode == "device":
+        assert dev.info()["n_nodes"] < host.info()["n_nodes"]  # one shared tree per mesh instead of reference + traversal tree
     ora = orc.OracleScene(scene).trace_batch(rays, seed=4)
     assert (ora["object"] != A.RTR_NO_HIT).mean() > 0.05
     for flags in (0, A.FLAG_EXHAUSTIVE, A.FLAG_REFERENCE_TREE, A.FLAG_REFERENCE_TREE | A.FLAG_EXHAUSTIVE, A.FLAG_COUNT_WORK):
@@ -159,10 +163,12 @@ def test_device_mesh_build_is_faster_to_upload_on_a_large_mesh(ctx):
     s = rt.Scene.default()
     lam = s.add_material(rt.Lambertian(rt.Color(0.6, 0.5, 0.4)))
     s.add_object(random_triangle_mesh(200_000, 7, lam))
-    dev, host = upload(ctx, s, "device"), upload(ctx, s, "host")
+    dev, hyb, host = upload(ctx, s, "device"), upload(ctx, s, "hybrid"), upload(ctx, s, "host")
     assert dev.info()["build_ms"] < 0.5 * host.info()["build_ms"], (dev.info()["build_ms"], host.info()["build_ms"])
+    assert hyb.info()["build_ms"] < 0.7 * host.info()["build_ms"], (hyb.info()["build_ms"], host.info()["build_ms"])
     rays = _scenes.random_rays(1 << 16, 9, 3.0)
     assert dev.trace_batch(rays).tobytes() == host.trace_batch(rays).tobytes()
+    assert hyb.trace_batch(rays).tobytes() == host.trace_batch(rays).tobytes()
 
 
 def test_device_mesh_build_rejects_nan_like_the_reference_panics(ctx):
