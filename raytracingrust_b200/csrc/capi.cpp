@@ -90,6 +90,9 @@ static rtr_status context_init(rtr_context* ctx, int device, void* stream) {
     else { CU(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)); ctx->own_stream = true; }
     CU(cudaEventCreate(&ctx->ev0));
     CU(cudaEventCreate(&ctx->ev1));
+    for (cudaStream_t& ls : ctx->lane_stream) CU(cudaStreamCreateWithFlags(&ls, cudaStreamNonBlocking));
+    for (cudaEvent_t& ev : ctx->wf_ev_wave) CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ctx->wf_ev_fork, cudaEventDisableTiming));
     CU(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
     {
         cudaMemPoolProps props;
@@ -121,10 +124,12 @@ static rtr_status context_init(rtr_context* ctx, int device, void* stream) {
         ctx->wf_bin_keys = v <= 0 ? 0u : v <= 8 ? 8u : 24u;
     }
     if (const char* e = std::getenv("RTR_WF_WIDE")) ctx->wf_wide4 = std::atoi(e) != 0;
+    if (const char* e = std::getenv("RTR_WF_LANES")) ctx->wf_lanes = (uint32_t)std::min<int>(std::max(1, std::atoi(e)), (int)rtr_context::kMaxLanes);
+    if (const char* e = std::getenv("RTR_WF_LANES_MIN_DEPTH")) ctx->wf_lanes_min_depth = (uint32_t)std::max(0, std::atoi(e));
     if (const char* e = std::getenv("RTR_WF_BIN_LAST")) ctx->wf_bin_last_bounce = (uint32_t)std::max(0, std::atoi(e));
     if (const char* e = std::getenv("RTR_SCAN_KERNEL")) ctx->use_scan_kernel = std::atoi(e);
     CU(cudaMalloc((void**)&ctx->work_counter, sizeof(uint32_t)));
-    CU(cudaMalloc((void**)&ctx->wf_counters, WFC_WORDS * sizeof(uint32_t)));
+    CU(cudaMalloc((void**)&ctx->wf_counters, rtr_context::kMaxLanes * WFC_WORDS * sizeof(uint32_t)));
     CU(cudaMalloc((void**)&ctx->stats, STAT_COUNT * sizeof(unsigned long long)));
     return RTR_OK;
 }
@@ -154,6 +159,9 @@ void rtr_context_destroy(rtr_context* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    for (cudaStream_t ls : ctx->lane_stream) if (ls) { cudaStreamSynchronize(ls); cudaStreamDestroy(ls); }
+    for (cudaEvent_t ev : ctx->wf_ev_wave) if (ev) cudaEventDestroy(ev);
+    if (ctx->wf_ev_fork) cudaEventDestroy(ctx->wf_ev_fork);
     cudaFree(ctx->wf_state); cudaFree(ctx->wf_counters);
     cudaFree(ctx->work_counter); cudaFree(ctx->stats); cudaFree(ctx->accum); cudaFree(ctx->partials);
     cudaFree(ctx->rgba); cudaFree(ctx->batch_in); cudaFree(ctx->batch_in2); cudaFree(ctx->batch_out);
@@ -440,29 +448,28 @@ rtr_status rtr::check_render_args(rtr_context* ctx, const rtr_scene* scene, cons
 }
 
 // ------------------------------------------------------------------ wavefront variant (wavefront.cu)
-// One wave = generate, max_ray_depth x [extend, shade+compact], ordered sample sum, next-wave bookkeeping.
+// One wave = generate, max_ray_depth x [extend, shade+compact] (this function), then the ordered sample sum and the
+// next-wave bookkeeping (launch_wf_end_wave, issued by the caller so that it can be ordered across wave sequences).
 // Every queue size lives on the device, so the launch sequence of a wave is fixed: it is captured into a
 // CUDA graph once per call and replayed for each wave (plain launches when capture or instantiation fails).
 static cudaError_t wf_launch_wave(rtr_context* ctx, WfArgs a, const WfPaths buf[2], bool exhaustive, bool count_work,
-                                  int gen_grid, int ext_grid, int shade_grid, int sum_grid, int bin_grid, uint32_t* launches) {
+                                  int gen_grid, int ext_grid, int shade_grid, int bin_grid, cudaStream_t st, uint32_t* launches) {
     cudaError_t e = cudaSuccess;
     auto step = [&](cudaError_t r) { if (e == cudaSuccess) e = r; ++*launches; };
     a.bounce = 0; a.in = buf[0]; a.out = buf[1];
-    step(launch_wf_generate(a, gen_grid, ctx->stream));
+    step(launch_wf_generate(a, gen_grid, st));
     uint32_t* const perm = a.perm_out;
     for (uint32_t b = 0; b < a.max_ray_depth; ++b) {
         a.bounce = b; a.in = buf[b & 1]; a.out = buf[(b + 1) & 1];
         a.perm = nullptr;
         // camera rays arrive in tile order and are coherent as they are; scattered rays are regrouped by direction
         if (perm && b >= 1 && b <= ctx->wf_bin_last_bounce) {
-            step(launch_wf_bin(a, bin_grid, ctx->stream));
+            step(launch_wf_bin(a, bin_grid, st));
             a.perm = perm;
         }
-        step(launch_wf_extend(a, ext_grid, exhaustive, count_work, ctx->stream));
-        step(launch_wf_shade(a, shade_grid, count_work, ctx->stream));
+        step(launch_wf_extend(a, ext_grid, exhaustive, count_work, st));
+        step(launch_wf_shade(a, shade_grid, count_work, st));
     }
-    step(launch_wf_end_wave(a, sum_grid, ctx->stream));
-    if (a.lbuf) ++*launches;
     return e;
 }
 
@@ -493,28 +500,48 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     if (ws < 1) ws = 1;
     if (ws > count) ws = count ? count : 1;
     if (ws > 0xFFFFFFull) ws = 0xFFFFFFull;  // (sample - wave_begin) is packed into 24 bits
+    // Two wave sequences (context.h wf_lanes): the waves alternate between two streams, each with its own path state and
+    // queue counters, so that one wave's launch tails and thin late bounces overlap the other's full kernels.
+    uint32_t lanes = 1;
+    if (ctx->wf_lanes >= 2 && a.max_ray_depth >= ctx->wf_lanes_min_depth && count >= 2 && n_pixels > 0) {
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(ctx->stream, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) lanes = std::min<uint32_t>(ctx->wf_lanes, count);
+        else (void)cudaGetLastError();
+    }
+    // each sequence keeps the full wave size (2 x 2.1 GB of path state: bigger waves AND overlap measured best,
+    // profiles/r2/ab_wave_sequences_sizes.txt); a render of less than two such waves is cut into two
+    if (lanes > 1 && ws > (count + lanes - 1u) / lanes) ws = (count + lanes - 1u) / lanes;
     a.wave_samples = (uint32_t)ws;
+    a.wave_step = lanes;
     const uint64_t n_paths = ws * n_pixels;
     if (n_paths > 0x7FFFFFFFull) return fail(ctx, RTR_INVALID_ARG, "wavefront: too many paths per wave");
     const uint32_t n_waves = count ? (uint32_t)((count + ws - 1) / ws) : 0;
-    const bool use_lbuf = ws > 1;
+    const bool use_lbuf = ws > 1 || lanes > 1;  // several sequences: each wave's samples wait in lbuf for their turn in the pixel sums
     // direction binning (wavefront.cu wf_bin_kernel): BVH walks only, and only when a bounce follows the first
     const bool use_bin = ctx->wf_bin_keys != 0u && a.enable_bvh_tree != 0u && a.max_ray_depth > 1u && n_paths >= RTR_WF_BIN_BLOCK;
     const size_t streams = 7 + (use_lbuf ? 1 : 0);
     const size_t perm_elems = use_bin ? ((size_t)n_paths + 3) / 4 : 0;  // n_paths uint32 in float4 units
-    CU(grow(&ctx->wf_state, &ctx->wf_state_elems, streams * (size_t)n_paths + perm_elems));
-    WfPaths buf[2];
-    float4* s0 = ctx->wf_state;
-    buf[0].o = s0; buf[0].d = s0 + n_paths; buf[0].thr = s0 + 2 * n_paths;
-    buf[1].o = s0 + 3 * n_paths; buf[1].d = s0 + 4 * n_paths; buf[1].thr = s0 + 5 * n_paths;
-    a.hit = s0 + 6 * n_paths;
-    a.lbuf = use_lbuf ? s0 + 7 * n_paths : nullptr;
-    a.perm = nullptr;
-    a.perm_out = use_bin ? reinterpret_cast<uint32_t*>(s0 + streams * (size_t)n_paths) : nullptr;
-    a.bin_keys = ctx->wf_bin_keys;
-    a.accum = accum_dev;
-    a.counters = ctx->wf_counters;
-    a.stats = ctx->stats;
+    const size_t lane_elems = streams * (size_t)n_paths + perm_elems;
+    CU(grow(&ctx->wf_state, &ctx->wf_state_elems, lanes * lane_elems));
+    constexpr uint32_t ML = rtr_context::kMaxLanes;
+    WfArgs la[ML];
+    WfPaths buf[ML][2];
+    cudaStream_t lst[ML] = {ctx->stream, ctx->lane_stream[0], ctx->lane_stream[1], ctx->lane_stream[2]};
+    for (uint32_t l = 0; l < lanes; ++l) {
+        float4* s0 = ctx->wf_state + l * lane_elems;
+        buf[l][0].o = s0; buf[l][0].d = s0 + n_paths; buf[l][0].thr = s0 + 2 * n_paths;
+        buf[l][1].o = s0 + 3 * n_paths; buf[l][1].d = s0 + 4 * n_paths; buf[l][1].thr = s0 + 5 * n_paths;
+        la[l] = a;
+        la[l].hit = s0 + 6 * n_paths;
+        la[l].lbuf = use_lbuf ? s0 + 7 * n_paths : nullptr;
+        la[l].perm = nullptr;
+        la[l].perm_out = use_bin ? reinterpret_cast<uint32_t*>(s0 + streams * (size_t)n_paths) : nullptr;
+        la[l].bin_keys = ctx->wf_bin_keys;
+        la[l].accum = accum_dev;
+        la[l].counters = ctx->wf_counters + l * WFC_WORDS;
+        la[l].stats = ctx->stats;
+        la[l].wave_first = l;
+    }
     const int per_sm = wf_extend_max_blocks_per_sm(exhaustive, count_work, a.sc.n_volumes != 0u || a.enable_bvh_tree == 0u, false, wf_extend_wide4(a, exhaustive, count_work));
     if (per_sm <= 0) return fail(ctx, RTR_CUDA_ERROR, "wf_extend cannot be resident on this device");
     auto blocks_for = [&](uint64_t items, int cap_per_sm) {
@@ -530,39 +557,56 @@ static rtr_status render_wavefront(rtr_context* ctx, const rtr_scene* scene, con
     if (reset_stats) CU(cudaMemsetAsync(ctx->stats, 0, STAT_COUNT * sizeof(unsigned long long), ctx->stream));
     uint32_t launches = 0;
     if (timed) CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    CU(launch_wf_begin(a, ctx->stream));
+    CU(launch_wf_begin(la[0], ctx->stream));
     ++launches;
-    bool done = false;
-    if (ctx->wf_use_graph && n_waves > 1) {
-        cudaGraph_t graph = nullptr;
-        cudaGraphExec_t exec = nullptr;
-        uint32_t per_wave = 0;
-        cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
+    if (lanes > 1) {  // the other sequences start once the image and the counters are clear
+        for (uint32_t l = 1; l < lanes; ++l) { CU(launch_wf_begin_lane(la[l], ctx->stream)); ++launches; }
+        CU(cudaEventRecord(ctx->wf_ev_fork, ctx->stream));
+        for (uint32_t l = 1; l < lanes; ++l) CU(cudaStreamWaitEvent(lst[l], ctx->wf_ev_fork, 0));
+    }
+    // the launch sequence of one wave, per lane: a CUDA graph when there is something to replay
+    cudaGraph_t graph[ML] = {nullptr, nullptr, nullptr, nullptr};
+    cudaGraphExec_t exec[ML] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t per_wave = 0;
+    bool use_graph = ctx->wf_use_graph && n_waves > lanes;
+    for (uint32_t l = 0; l < lanes && use_graph; ++l) {
+        per_wave = 0;
+        cudaError_t e = cudaStreamBeginCapture(lst[l], cudaStreamCaptureModeThreadLocal);
         if (e == cudaSuccess) {
-            cudaError_t le = wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, bin_grid, &per_wave);
-            e = cudaStreamEndCapture(ctx->stream, &graph);  // always ends the capture, also after a failed launch
+            cudaError_t le = wf_launch_wave(ctx, la[l], buf[l], exhaustive, count_work, gen_grid, ext_grid, shade_grid, bin_grid, lst[l], &per_wave);
+            e = cudaStreamEndCapture(lst[l], &graph[l]);  // always ends the capture, also after a failed launch
             if (e == cudaSuccess && le != cudaSuccess) e = le;
         }
-        if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
-        if (e == cudaSuccess) {
-            // from here on work is in flight: a failing launch is an error, not a reason to start over
-            for (uint32_t w = 0; w < n_waves && e == cudaSuccess; ++w) e = cudaGraphLaunch(exec, ctx->stream);
-            if (exec) cudaGraphExecDestroy(exec);
-            if (graph) cudaGraphDestroy(graph);
-            if (e != cudaSuccess) return cuda_fail(ctx, e, "wavefront graph launch");
-            launches += per_wave * n_waves;
-            done = true;
-        } else {
+        if (e == cudaSuccess) e = cudaGraphInstantiate(&exec[l], graph[l], 0);
+        if (e != cudaSuccess) {
             // capture / instantiation is unavailable here (e.g. the caller's stream is itself being captured): nothing
-            // has run yet, so clear the error and issue the same sequence as plain launches below
-            if (exec) cudaGraphExecDestroy(exec);
-            if (graph) cudaGraphDestroy(graph);
+            // of a wave has run yet, so clear the error and issue the same sequences as plain launches
+            use_graph = false;
             (void)cudaGetLastError();
         }
     }
-    if (!done)
-        for (uint32_t w = 0; w < n_waves; ++w)
-            CU(wf_launch_wave(ctx, a, buf, exhaustive, count_work, gen_grid, ext_grid, shade_grid, sum_grid, bin_grid, &launches));
+    cudaError_t we = cudaSuccess;
+    for (uint32_t w = 0; w < n_waves && we == cudaSuccess; ++w) {
+        const uint32_t l = w % lanes;
+        if (use_graph) { we = cudaGraphLaunch(exec[l], lst[l]); launches += per_wave; }
+        else we = wf_launch_wave(ctx, la[l], buf[l], exhaustive, count_work, gen_grid, ext_grid, shade_grid, bin_grid, lst[l], &launches);
+        // pixel sums in wave order (render.rs:99 adds the samples of a pixel one after the other): this wave's sum waits
+        // for the previous wave's, which ran on the other stream
+        if (we == cudaSuccess && lanes > 1 && w > 0) we = cudaStreamWaitEvent(lst[l], ctx->wf_ev_wave[(w - 1) % ML], 0);
+        if (we == cudaSuccess) we = launch_wf_end_wave(la[l], sum_grid, lst[l]);
+        launches += la[l].lbuf ? 2u : 1u;
+        if (we == cudaSuccess && lanes > 1) we = cudaEventRecord(ctx->wf_ev_wave[w % ML], lst[l]);
+    }
+    // join: the last wave's sum is ordered after every earlier one; if it ran on another stream, wait for it
+    if (we == cudaSuccess && lanes > 1 && n_waves > 0 && ((n_waves - 1) % lanes) != 0) we = cudaStreamWaitEvent(ctx->stream, ctx->wf_ev_wave[(n_waves - 1) % ML], 0);
+    for (uint32_t l = 0; l < ML; ++l) {
+        if (exec[l]) cudaGraphExecDestroy(exec[l]);
+        if (graph[l]) cudaGraphDestroy(graph[l]);
+    }
+    if (we != cudaSuccess) {
+        for (uint32_t l = 1; l < lanes; ++l) cudaStreamSynchronize(lst[l]);
+        return cuda_fail(ctx, we, "wavefront wave launch");
+    }
     if (timed) CU(cudaEventRecord(ctx->ev1, ctx->stream));
     if (stats_out) {
         std::memset(stats_out, 0, sizeof(*stats_out));

@@ -29,9 +29,17 @@ struct rtr_context {
     float4* partials = nullptr; size_t partials_elems = 0;
     uchar4* rgba = nullptr; size_t rgba_pixels = 0;
     float4* wf_state = nullptr; size_t wf_state_elems = 0;  // wavefront: 7 path streams (+ lbuf), see render_wavefront
-    uint32_t* wf_counters = nullptr;
+    uint32_t* wf_counters = nullptr;    // kMaxLanes x WFC_WORDS: one block per wave sequence
+    static constexpr uint32_t kMaxLanes = 4;
+    cudaStream_t lane_stream[kMaxLanes - 1] = {nullptr, nullptr, nullptr};  // the further wave sequences of a wavefront render (RTR_WF_LANES)
+    cudaEvent_t wf_ev_wave[kMaxLanes] = {nullptr, nullptr, nullptr, nullptr}, wf_ev_fork = nullptr;
+    // RTR_WF_LANES: 2 = consecutive waves run as two launch sequences on two streams, so that the launch tails and the thin
+    // late bounces of one wave (few paths alive, each launch waiting on its longest walk) overlap the full kernels of the
+    // other; the per-pixel sums stay in wave order (events), so the image is bit-identical.  With 2^25-path waves: +3.0..+5.0 %
+    // on C1 / C3 / C4 / C5, +36 % on the depth-50 mesh bench (profiles/r2/ab_wave_sequences*.txt; 3 and 4 sequences add little).  Used from max_ray_depth >= wf_lanes_min_depth (RTR_WF_LANES_MIN_DEPTH).
+    uint32_t wf_lanes = 2, wf_lanes_min_depth = 1;
     uint32_t wf_refill_threshold = 16;  // RTR_WF_REFILL_THRESHOLD
-    uint64_t wf_target_paths = 1ull << 24;  // RTR_WF_PATHS: paths in flight per wave (swept 2^22..2^25 on B200; 2.1 GB of path state)
+    uint64_t wf_target_paths = 1ull << 25;  // RTR_WF_PATHS: paths in flight per wave and sequence (4.3 GB of path state each; swept 2^22..2^25 with one and with several sequences on B200)
     int wf_use_graph = 1;  // RTR_WF_GRAPH
     // Same-address atomics run at ~1 per ns on B200 (ncu, profiles/r2: wf_generate issued 24 % of its slots and used 19 % of
     // DRAM while doing 512 K atomicAdds on the queue counter in 0.48 ms).  RTR_WF_ATOMICS: bit 0 = atomic-free wf_generate

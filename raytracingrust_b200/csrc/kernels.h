@@ -127,6 +127,7 @@ struct WfArgs {
     uint32_t k0, k1;
     uint32_t sample_begin, sample_end;  // this call's global sample range
     uint32_t wave_samples;              // samples of every pixel in flight per wave
+    uint32_t wave_first, wave_step;     // this launch sequence renders waves wave_first, wave_first + wave_step, ... (two sequences overlap: capi.cpp)
     uint32_t bounce;                    // which [extend, shade] pair this launch is
     uint32_t refill_threshold;          // extend refills idle lanes when fewer lanes than this are walking
     uint32_t atomics_mode;              // bit 0: wf_generate hands out slots without atomics when the image tiles exactly;
@@ -152,6 +153,7 @@ cudaError_t launch_wf_generate(const WfArgs& a, int grid, cudaStream_t st);
 cudaError_t launch_wf_extend(const WfArgs& a, int grid, bool exhaustive, bool count, cudaStream_t st);
 cudaError_t launch_wf_shade(const WfArgs& a, int grid, bool count, cudaStream_t st);
 int wf_shade_threads();  // CTA size of wf_shade (grid sizing)
+cudaError_t launch_wf_begin_lane(const WfArgs& a, cudaStream_t st);  // the counters of a second wave sequence only
 cudaError_t launch_wf_end_wave(const WfArgs& a, int grid, cudaStream_t st);  // ordered sum of lbuf + advance the wave
 // rtr_trace_batch = unpack (AoS rays -> the wavefront's ray streams, queue size n) -> wf_extend (the render's own
 // persistent, majority-rule, short-stack walk) -> finish (HitRecord of every winner -> AoS rtr_hit)

@@ -69,7 +69,7 @@ __device__ __forceinline__ void finish_sample(const WfArgs& a, uint32_t pixel, u
 __global__ void wf_begin_kernel(const WfArgs a) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < a.n_pixels && !a.accumulate) a.accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-    if (i < WFC_WORDS) a.counters[i] = 0u;
+    if (i < WFC_WORDS) a.counters[i] = i == (uint32_t)WFC_WAVE ? a.wave_first : 0u;
 }
 
 // ------------------------------------------------------------------ generate
@@ -480,7 +480,7 @@ __global__ void wf_next_wave_kernel(const WfArgs a) {
     if (rays) atomicAdd(&a.stats[STAT_RAYS], rays);
     __syncthreads();
     for (uint32_t i = WFC_QCOUNT + threadIdx.x; i < WFC_WORDS; i += blockDim.x) a.counters[i] = 0u;
-    if (threadIdx.x == 0) a.counters[WFC_WAVE] += 1u;
+    if (threadIdx.x == 0) a.counters[WFC_WAVE] += a.wave_step;
 }
 
 // ------------------------------------------------------------------ rtr_trace_batch on the wavefront walk
@@ -566,6 +566,13 @@ int wf_extend_max_blocks_per_sm(bool exhaustive, bool count, bool volumes, bool 
 cudaError_t launch_wf_begin(const WfArgs& a, cudaStream_t st) {
     const uint32_t n = a.n_pixels > (uint32_t)WFC_WORDS ? a.n_pixels : (uint32_t)WFC_WORDS;
     wf_begin_kernel<<<(n + 255) / 256, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_wf_begin_lane(const WfArgs& a, cudaStream_t st) {
+    WfArgs b = a;
+    b.n_pixels = 0;  // counters only: the image is cleared by the first sequence's wf_begin
+    wf_begin_kernel<<<(WFC_WORDS + 255) / 256, 256, 0, st>>>(b);
     return cudaGetLastError();
 }
 
