@@ -419,7 +419,7 @@ class Bench:
             "config": {"workload": desc, "kernel": used, "per_gpu_spp": s_count, "image_spp": total_spp,
                        "parallelism": f"sample-slices x{world} + ncclReduce",
                        "l2_policy": "each step rewrites the accumulation buffer and traces fresh Philox paths; the wavefront "
-                                    "streams 2 GB of path state per wave (> the 126 MB L2); scene geometry is L2-resident by design (SURVEY 8d)",
+                                    "streams 4 GB of path state per wave, two waves in flight (> the 126 MB L2); scene geometry is L2-resident by design (SURVEY 8d)",
                        "scene_device_bytes": info["device_bytes"], "bvh_nodes": info["n_nodes"],
                        "warmup_spp": w_spp},
             "clocks": clocks,
@@ -535,7 +535,7 @@ def main():
     subs = {}
     if not args.no_workloads and args.workload == "benchmark":
         for name, steps, cap, e2e_spp in SUB_WORKLOADS:
-            rec = b.measure(name, steps, 3, spp_cap=cap, e2e_spp=e2e_spp, warmup_spp=max(1, min(16, (1 << 26) // (WORKLOADS[name]["W"] * WORKLOADS[name]["H"]))))
+            rec = b.measure(name, steps, 3, spp_cap=cap, e2e_spp=e2e_spp, warmup_spp=max(1, min(64, (1 << 26) // (WORKLOADS[name]["W"] * WORKLOADS[name]["H"]))))  # two full 2^25-path waves: the warm-up allocates the path state the timed steps use
             if rec is not None:
                 subs[name] = rec
     if not args.no_workloads and args.workload == "benchmark":
