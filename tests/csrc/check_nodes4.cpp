@@ -43,7 +43,65 @@ static int compare(const HostFlat& f, uint32_t e2, uint32_t e4, const char* what
     for (const B6& x : ib) if (!ia.count(x)) { std::printf("FAIL %s: interior box not in the 2-wide tree\n", what); return 1; }
     return 0;
 }
+// brute-force counterparts of count_nodes4 / count_gated (host_flatten.h): walk the median-split shape node by node
+static uint32_t brute_nodes4(uint32_t n, uint32_t depth) {
+    if (n < 2) return 0;
+    return (((depth & 1u) == 0u && (n >= 3 || depth == 0)) ? 1u : 0u) + brute_nodes4(n / 2, depth + 1) + brute_nodes4(n - n / 2, depth + 1);
+}
+static uint32_t brute_gated(uint32_t n) { return n <= 2 ? (n ? 1u : 0u) : brute_gated(n / 2) + brute_gated(n - n / 2); }
+static int check_counts() {
+    int bad = 0;
+    for (uint32_t n = 1; n <= 70000; n = n < 3000 ? n + 1 : n + n / 7 + 1) {
+        if (n >= 2 && count_nodes4(n) != brute_nodes4(n, 0)) { std::printf("FAIL count_nodes4(%u) = %u, expected %u\n", n, count_nodes4(n), brute_nodes4(n, 0)); ++bad; }
+        if (count_gated(n) != brute_gated(n)) { std::printf("FAIL count_gated(%u) = %u, expected %u\n", n, count_gated(n), brute_gated(n)); ++bad; }
+    }
+    return bad;
+}
+
+// the hybrid build's host half: a SAH tree + 4-wide collapse over gated entries reaches every entry exactly once
+static int check_over_gates() {
+    std::mt19937 g(11); std::uniform_real_distribution<float> U(-5.f, 5.f), R(0.01f, 0.5f);
+    const uint32_t n = 5003, base = 777, base4 = 333;
+    std::vector<F4> gated(2 * (size_t)n);
+    std::multiset<uint32_t> want;
+    for (uint32_t p = 0; p < n; ++p) {
+        const bool second_of_pair = p > 0 && (p % 5u) == 1u;  // position p-1 holds a paired entry
+        uint32_t ref = second_of_pair ? REF_EMPTY_VALUE : RTR_MAKE_REF((p % 5u) == 0u && p + 1 < n ? REF_TRI2 : REF_TRI, p);
+        if ((p % 5u) == 0u && p + 1 >= n) ref = RTR_MAKE_REF(REF_TRI, p);
+        const float c[3] = {U(g), U(g), U(g)}, r = R(g);
+        float w; std::memcpy(&w, &ref, 4);
+        gated[2 * (size_t)p] = F4{c[0] - r, c[1] - r, c[2] - r, w};
+        gated[2 * (size_t)p + 1] = F4{c[0] + r, c[1] + r, c[2] + r, 0.0f};
+        if (ref != REF_EMPTY_VALUE) want.insert(ref);
+    }
+    std::vector<F4> nodes, nodes4;
+    uint32_t depth = 0, d4 = 0;
+    build_traversal_over_gates(gated.data(), n, base, base4, 8, nodes, nodes4, &depth, &d4);
+    int bad = 0;
+    if (nodes.size() / 4 != want.size() - 1) { std::printf("FAIL over gates: %zu nodes for %zu entries\n", nodes.size() / 4, want.size()); ++bad; }
+    std::multiset<uint32_t> got2, got4;
+    std::vector<uint32_t> stack{RTR_MAKE_REF(REF_NODE, base)};
+    while (!stack.empty()) {
+        const uint32_t ref = stack.back(); stack.pop_back();
+        if (RTR_REF_KIND(ref) != REF_NODE) { got2.insert(ref); continue; }
+        const F4* q = &nodes[(size_t)(RTR_REF_INDEX(ref) - base) * 4];
+        for (int k = 0; k < 2; ++k) { const uint32_t c = bitsof(q[k].w); if (c != REF_EMPTY_VALUE) stack.push_back(c); }
+    }
+    stack.push_back(RTR_MAKE_REF(REF_NODE, base4));
+    while (!stack.empty()) {
+        const uint32_t ref = stack.back(); stack.pop_back();
+        if (RTR_REF_KIND(ref) != REF_NODE) { got4.insert(ref); continue; }
+        const F4* q = &nodes4[(size_t)(RTR_REF_INDEX(ref) - base4) * 8];
+        for (int k = 0; k < 4; ++k) { const uint32_t c = bitsof(q[k].w); if (c != REF_EMPTY_VALUE) stack.push_back(c); }
+    }
+    if (got2 != want) { std::printf("FAIL over gates: the 2-wide tree does not reach every entry once\n"); ++bad; }
+    if (got4 != want) { std::printf("FAIL over gates: the 4-wide tree does not reach every entry once\n"); ++bad; }
+    if (d4 > depth || depth > 13 + 8) { std::printf("FAIL over gates: depth %u / %u\n", depth, d4); ++bad; }
+    return bad;
+}
+
 int main() {
+    if (check_counts() || check_over_gates()) { std::printf("FAIL\n"); return 1; }
     std::mt19937 g(7); std::uniform_real_distribution<float> U(-10.f, 10.f), R(0.05f, 0.6f);
     std::vector<rtr_sphere> sph; std::vector<rtr_object_ref> obj; std::vector<rtr_mesh> meshes; std::vector<rtr_volume> vols;
     for (int i = 0; i < 1500; ++i) { sph.push_back({{U(g), U(g), U(g)}, R(g), 0}); obj.push_back({RTR_OBJ_SPHERE, (uint32_t)i}); }
