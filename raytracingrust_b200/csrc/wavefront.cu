@@ -29,6 +29,9 @@
 #ifndef RTR_WF_SHADE_MIN_BLOCKS
 #define RTR_WF_SHADE_MIN_BLOCKS 4  // wf_shade waits on memory (ncu: 3.8 long-scoreboard stalls per issue); swept 9 / 12 / 16
 #endif
+#ifndef RTR_WF_SHADE_PREFETCH
+#define RTR_WF_SHADE_PREFETCH 1  // +0.2..+0.7 % (profiles/r2/ab_shade_prefetch_occupancy.txt)
+#endif
 #ifndef RTR_WF_NODE_BURST
 #define RTR_WF_NODE_BURST 0  // 1: two node steps per scheduling decision
 #endif
@@ -376,6 +379,17 @@ __global__ void __launch_bounds__(RTR_WF_SHADE_THREADS, RTR_WF_SHADE_MIN_BLOCKS)
         Ray ray; ray.o = ray.d = mk(0.0f, 0.0f, 0.0f);
         v3 T = mk(0.0f, 0.0f, 0.0f);
         uint32_t pixel = 0, rel = 0, depth = 0;
+#if RTR_WF_SHADE_PREFETCH
+        {   // the next trip's four stream records towards L2 while this trip's dependent fetches (hit -> primitive -> material) run
+            const uint64_t nx = (uint64_t)i + (uint64_t)gridDim.x * blockDim.x;
+            if (nx < n && (threadIdx.x & 7u) == 0u) {  // one hint per 128-byte line
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.in.o + nx));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.in.d + nx));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.in.thr + nx));
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.hit + nx));
+            }
+        }
+#endif
         if (i < n) {
             const float4 o = a.in.o[i], d = a.in.d[i], t = a.in.thr[i], h = a.hit[i];
             ray.o = xyz(o); ray.d = xyz(d);
