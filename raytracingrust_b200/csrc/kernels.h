@@ -102,7 +102,7 @@ cudaError_t launch_camera_rays(const CameraBasis& cam, uint32_t W, uint32_t H, u
 #define RTR_WF_EXTEND_MIN_BLOCKS_W4 8        // the 4-wide instantiations (swept 6..8 with Volume::hit, 7..9 without: profiles/r2/ab_bvh4_variants.txt)
 #endif
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4
-#define RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4 8
+#define RTR_WF_EXTEND_MIN_BLOCKS_NOVOL_W4 9  // 56 registers, no spills; under two wave sequences +1..+2.5 % over 8 (profiles/r2/ab_extend_occupancy_two_sequences.txt)
 #endif
 #ifndef RTR_WF_EXTEND_MIN_BLOCKS_NOVOL
 #define RTR_WF_EXTEND_MIN_BLOCKS_NOVOL 9  // without it: 56 registers, swept 6..10 on B200 (9: +2..5 % over 8)
