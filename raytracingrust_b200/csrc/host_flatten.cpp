@@ -11,8 +11,12 @@
 #include "host_flatten.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <system_error>
+#include <thread>
 
 namespace rtr {
 
@@ -118,14 +122,33 @@ struct Flattener {
         return dx * dy + dy * dz + dz * dx;
     }
     struct FastOut { uint32_t ref; Box box; uint32_t depth; };
+    // helper threads a build may use besides its caller's: RTR_HOST_THREADS - 1, by default the host's cores (at most 15)
+    static int spare_threads() {
+        if (const char* e = std::getenv("RTR_HOST_THREADS")) return std::max(0, std::min(63, std::atoi(e) - 1));
+        const unsigned hw = std::thread::hardware_concurrency();
+        return (int)std::min(15u, hw > 1 ? hw - 1 : 0u);
+    }
     // min/max for the SAH BINS only: plain compare-select (minss / maxss).  The bins feed the cost heuristic; the boxes
     // written into the nodes are exact unions of the gates (surround), so NaN / signed-zero subtleties do not matter here.
     static Box surround_fast(const Box& a, const Box& b) {
         return Box{V3{a.min.x < b.min.x ? a.min.x : b.min.x, a.min.y < b.min.y ? a.min.y : b.min.y, a.min.z < b.min.z ? a.min.z : b.min.z},
                    V3{a.max.x > b.max.x ? a.max.x : b.max.x, a.max.y > b.max.y ? a.max.y : b.max.y, a.max.z > b.max.z ? a.max.z : b.max.z}};
     }
-    std::vector<GatedLeaf> part_scratch;  // stable partition buffer, grown once per collection
+    std::vector<GatedLeaf> part_scratch;  // stable partition buffer, as long as the collection: a range partitions through its own part
+    // A binary tree over n entries has n - 1 nodes, and the serial recursion numbers them in pre-order: node `idx` of the
+    // range [lo, hi) split at mid has its left subtree from idx + 1 and its right subtree from idx + (mid - lo).  With the
+    // indices known in advance the subtrees are independent: the top of a large tree is built by several threads, and
+    // the arrays come out byte for byte as the serial build writes them.
     FastOut build_traversal(std::vector<GatedLeaf>& L, size_t lo, size_t hi, uint32_t depth_left) {
+        const size_t n = hi - lo;
+        if (n == 1) return FastOut{L[lo].ref, L[lo].gate, L[lo].depth};
+        const uint32_t first = out.device_nodes + (uint32_t)(out.nodes.size() / 4);
+        out.nodes.resize(out.nodes.size() + 4 * (n - 1), F4{0, 0, 0, 0});
+        if (part_scratch.size() < L.size()) part_scratch.resize(L.size());
+        std::atomic<int> spare(spare_threads());
+        return build_traversal_at(L, lo, hi, depth_left, first, spare);
+    }
+    FastOut build_traversal_at(std::vector<GatedLeaf>& L, size_t lo, size_t hi, uint32_t depth_left, uint32_t idx, std::atomic<int>& spare) {
         const size_t n = hi - lo;
         if (n == 1) return FastOut{L[lo].ref, L[lo].gate, L[lo].depth};
         Box cb{L[lo].c, L[lo].c};  // centroid bounds
@@ -177,14 +200,14 @@ struct Flattener {
             if (best_axis >= 0) {
                 // stable partition into [bins <= plane][the rest] through the shared scratch buffer
                 const float mn = mn3[best_axis], scale = scale3[best_axis];
-                if (part_scratch.size() < n) part_scratch.resize(n);
+                GatedLeaf* scratch = part_scratch.data() + lo;
                 size_t nl = 0, nr = 0;
                 for (size_t i = lo; i < hi; ++i) {
                     const float c = best_axis == 0 ? L[i].c.x : best_axis == 1 ? L[i].c.y : L[i].c.z;
                     if (bin_of(c, mn, scale) <= best_plane) L[lo + nl++] = L[i];
-                    else part_scratch[nr++] = L[i];
+                    else scratch[nr++] = L[i];
                 }
-                for (size_t i = 0; i < nr; ++i) L[lo + nl + i] = part_scratch[i];
+                for (size_t i = 0; i < nr; ++i) L[lo + nl + i] = scratch[i];
                 const size_t m = lo + nl;
                 if (m > lo && m < hi) { mid = m; split_done = true; }
             }
@@ -195,9 +218,26 @@ struct Flattener {
                 return (axis == 0 ? a.c.x : axis == 1 ? a.c.y : a.c.z) < (axis == 0 ? b.c.x : axis == 1 ? b.c.y : b.c.z);
             });
         }
-        const uint32_t idx = alloc_node();
-        const FastOut l = build_traversal(L, lo, mid, depth_left - 1);
-        const FastOut r = build_traversal(L, mid, hi, depth_left - 1);
+        const uint32_t lidx = idx + 1u, ridx = idx + (uint32_t)(mid - lo);
+        FastOut l, r;
+        bool forked = false;
+        if (n >= 16384 && spare.fetch_sub(1) > 0) {
+            try {
+                std::thread t([&] { l = build_traversal_at(L, lo, mid, depth_left - 1, lidx, spare); });
+                forked = true;
+                r = build_traversal_at(L, mid, hi, depth_left - 1, ridx, spare);
+                t.join();
+            } catch (const std::system_error&) {  // no thread to be had: this range stays on the caller's
+                if (forked) throw;
+            }
+            spare.fetch_add(1);
+        } else if (n >= 16384) {
+            spare.fetch_add(1);
+        }
+        if (!forked) {
+            l = build_traversal_at(L, lo, mid, depth_left - 1, lidx, spare);
+            r = build_traversal_at(L, mid, hi, depth_left - 1, ridx, spare);
+        }
         write_node_raw(idx, l.ref, l.box, r.ref, r.box);
         return FastOut{RTR_MAKE_REF(REF_NODE, idx), surround(l.box, r.box), 1 + std::max(l.depth, r.depth)};
     }
@@ -267,15 +307,48 @@ struct Flattener {
         for (uint32_t h : handles) { c.hb[h] = coll.bounds(h); c.hc[h] = centroid(c.hb[h]); }
         c.list.swap(handles);
         c.kv.resize(n); c.tmp.resize(n);
+        // Phase 1, the O(n log^2 n) part: every node's stable sort.  The tree's shape is known beforehand (a node is a
+        // range, its children the two halves), a node's sort touches its own range only, so the subtrees of the upper
+        // levels are sorted by several threads.  Phase 2 (build_range) then walks the ranges in order, serially, and
+        // emits nodes, leaves, ranks and gates exactly as before.
+        std::atomic<int> spare(spare_threads());
+        std::atomic<bool> nan_key(false);
+        sort_range(c, 0, n, spare, nan_key);
+        if (nan_key.load()) { err = "NaN centroid (the reference panics at bvh.rs:99)"; return Built{REF_EMPTY_VALUE, Box{}, false, 0}; }
         return build_range(c, 0, n);
     }
-    Built build_range(BuildCtx& c, size_t lo, size_t hi) {
+    template <typename F, typename G>
+    static void fork_join(size_t n, std::atomic<int>& spare, F&& left, G&& right, size_t min_n = 4096) {  // left on another thread when one is spare
+        bool forked = false;
+        if (n >= min_n) {
+            if (spare.fetch_sub(1) > 0) {
+                try {
+                    std::thread t(left);
+                    forked = true;
+                    right();
+                    t.join();
+                } catch (const std::system_error&) {
+                    if (forked) throw;
+                }
+            }
+            spare.fetch_add(1);
+        }
+        if (!forked) { left(); right(); }
+    }
+    static void stable_sort_kv_mt(KV* a, KV* tmp, size_t n, std::atomic<int>& spare) {  // the same merge sort, halves in parallel
+        if (n < 65536) { stable_sort_kv(a, tmp, n); return; }
+        const size_t h = n / 2;
+        fork_join(n, spare, [&] { stable_sort_kv_mt(a, tmp, h, spare); }, [&] { stable_sort_kv_mt(a + h, tmp + h, n - h, spare); }, 65536);
+        size_t i = 0, j = h, o = 0;
+        while (i < h && j < n) tmp[o++] = (a[j].k < a[i].k) ? a[j++] : a[i++];
+        while (i < h) tmp[o++] = a[i++];
+        while (j < n) tmp[o++] = a[j++];
+        std::memcpy(a, tmp, n * sizeof(KV));
+    }
+    void sort_range(BuildCtx& c, size_t lo, size_t hi, std::atomic<int>& spare, std::atomic<bool>& nan_key) {
         const size_t n = hi - lo;
-        if (n == 0) return Built{REF_EMPTY_VALUE, Box{}, false, 0};  // BvhNode::None
-        if (n == 1) { Built b = c.coll->leaf(c.list[lo]); b.leaf = true; return b; }  // BvhNode::Object
+        if (n < 2) return;
         const uint32_t* L = c.list.data() + lo;
-        Box bounds = c.hb[L[0]];                                     // :68-72
-        for (size_t i = 1; i < n; ++i) bounds = surround(bounds, c.hb[L[i]]);
         Box cents{c.hc[L[0]], c.hc[L[0]]};                           // :75-79
         for (size_t i = 1; i < n; ++i) cents = surround(cents, Box{c.hc[L[i]], c.hc[L[i]]});
         const V3 spread = sub(cents.max, cents.min);
@@ -286,16 +359,27 @@ struct Flattener {
             const V3& ce = c.hc[L[i]];
             kv[i].k = axis == 0 ? ce.x : axis == 1 ? ce.y : ce.z;
             kv[i].h = L[i];
-            if (!(kv[i].k == kv[i].k)) { err = "NaN centroid (the reference panics at bvh.rs:99)"; return Built{REF_EMPTY_VALUE, Box{}, false, 0}; }
+            if (!(kv[i].k == kv[i].k)) { nan_key.store(true); return; }  // partial_cmp(..).unwrap() panics (bvh.rs:99)
         }
-        stable_sort_kv(kv, c.tmp.data() + lo, n);
+        stable_sort_kv_mt(kv, c.tmp.data() + lo, n, spare);
         for (size_t i = 0; i < n; ++i) c.list[lo + i] = kv[i].h;    // first n/2 left, the rest right (:125-134)
+        const size_t mid = lo + n / 2;
+        fork_join(n, spare, [&] { sort_range(c, lo, mid, spare, nan_key); }, [&] { sort_range(c, mid, hi, spare, nan_key); });
+    }
+    Built build_range(BuildCtx& c, size_t lo, size_t hi) {
+        const size_t n = hi - lo;
+        if (n == 0) return Built{REF_EMPTY_VALUE, Box{}, false, 0};  // BvhNode::None
+        if (n == 1) { Built b = c.coll->leaf(c.list[lo]); b.leaf = true; return b; }  // BvhNode::Object
         const size_t mid = lo + n / 2;
         uint32_t idx = alloc_node();  // pre-order index: a subtree is contiguous in memory
         Built l = build_range(c, lo, mid);
         if (!err.empty()) return l;
         Built r = build_range(c, mid, hi);
         if (!err.empty()) return r;
+        // bounds of the Split (:68-72): the reference folds surround() over the whole list at every node; min / max are
+        // associative, so the union of the two halves' bounds is the same box (up to the sign of a zero, which nothing
+        // observes) at O(n) instead of O(n log n) for the tree
+        const Box bounds = surround(mid - lo == 1 ? c.hb[c.list[lo]] : l.box, hi - mid == 1 ? c.hb[c.list[mid]] : r.box);
         write_node(idx, l, r);
         std::vector<GatedLeaf>* gated = c.gated;
         // a leaf child of this Split is gated by this Split's box
@@ -456,6 +540,11 @@ struct Flattener {
             return b;
         }
         MeshColl coll(*this, m, object);
+        {   // the mesh's records are appended one triangle at a time: make room once
+            const size_t nt = m.n_indices / 3;
+            out.tris.reserve(out.tris.size() + 4 * nt); out.tri_vn.reserve(out.tri_vn.size() + 3 * nt);
+            out.tri_info.reserve(out.tri_info.size() + nt); out.nodes.reserve(out.nodes.size() + 4 * (2 * nt + 4));
+        }
         std::vector<uint32_t> handles(m.n_indices / 3);
         for (size_t i = 0; i < handles.size(); ++i) handles[i] = (uint32_t)i;
         return build_collection(handles, coll);  // mesh.build_bvh() (mesh.rs:119-121)

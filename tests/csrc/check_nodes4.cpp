@@ -1,7 +1,9 @@
 // Host-only check of the 4-wide traversal tree (flat.h): below every entry point it must reach exactly the leaf slots the
 // 2-wide traversal tree reaches, each carrying the same box, and every interior slot's box must be one the 2-wide tree holds.
 // Built and run by tests/test_nodes4.py (g++ on this file + csrc/host_flatten.cpp; no GPU).
+#include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <random>
@@ -100,8 +102,36 @@ static int check_over_gates() {
     return bad;
 }
 
+// the host build's helper threads (RTR_HOST_THREADS) must not change a byte of the flattened scene
+static int check_threads() {
+    std::mt19937 g(3); std::uniform_real_distribution<float> U(-10.f, 10.f), R(0.05f, 0.3f);
+    const int ntri = 70001;
+    std::vector<float> pos, nrm; std::vector<uint32_t> idx;
+    for (int t = 0; t < ntri; ++t) { float c[3] = {U(g), U(g), std::round(U(g))}; for (int k = 0; k < 3; ++k) { for (int a = 0; a < 3; ++a) { pos.push_back(c[a] + (a == 2 ? 0.f : R(g))); nrm.push_back(a == 1); } idx.push_back(t * 3 + k); } }
+    rtr_mesh m{pos.data(), nrm.data(), idx.data(), (uint32_t)(pos.size() / 3), (uint32_t)idx.size(), 0, 0};
+    rtr_object_ref o{RTR_OBJ_MESH, 0};
+    rtr_material mat; std::memset(&mat, 0, sizeof(mat));
+    rtr_scene_desc d; std::memset(&d, 0, sizeof(d));
+    d.objects = &o; d.n_objects = 1; d.meshes = &m; d.n_meshes = 1; d.materials = &mat; d.n_materials = 1;
+    HostFlat f[2];
+    const char* threads[2] = {"1", "8"};
+    for (int k = 0; k < 2; ++k) {
+        setenv("RTR_HOST_THREADS", threads[k], 1);
+        std::string err;
+        if (flatten_scene(d, f[k], err, 8) != 0) { std::printf("FAIL threads: %s\n", err.c_str()); return 1; }
+    }
+    unsetenv("RTR_HOST_THREADS");
+    auto same = [](const std::vector<F4>& a, const std::vector<F4>& b) { return a.size() == b.size() && std::memcmp(a.data(), b.data(), a.size() * sizeof(F4)) == 0; };
+    if (!same(f[0].nodes, f[1].nodes) || !same(f[0].nodes4, f[1].nodes4) || !same(f[0].tris, f[1].tris) || !same(f[0].tri_vn, f[1].tri_vn) ||
+        f[0].root_entry != f[1].root_entry || f[0].root_entry4 != f[1].root_entry4 || f[0].max_depth != f[1].max_depth) {
+        std::printf("FAIL threads: the flattened scene depends on the thread count\n");
+        return 1;
+    }
+    return 0;
+}
+
 int main() {
-    if (check_counts() || check_over_gates()) { std::printf("FAIL\n"); return 1; }
+    if (check_counts() || check_over_gates() || check_threads()) { std::printf("FAIL\n"); return 1; }
     std::mt19937 g(7); std::uniform_real_distribution<float> U(-10.f, 10.f), R(0.05f, 0.6f);
     std::vector<rtr_sphere> sph; std::vector<rtr_object_ref> obj; std::vector<rtr_mesh> meshes; std::vector<rtr_volume> vols;
     for (int i = 0; i < 1500; ++i) { sph.push_back({{U(g), U(g), U(g)}, R(g), 0}); obj.push_back({RTR_OBJ_SPHERE, (uint32_t)i}); }

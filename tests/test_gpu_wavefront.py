@@ -62,15 +62,18 @@ def test_wavefront_bit_identical_to_megakernel(ctx, name, W, H, spp):
 
 
 def test_wavefront_wave_sizes_and_graph_replay_do_not_change_the_image():
-    """One sample per wave (direct accumulation), many samples per wave (per-sample buffer + ordered sum), a ragged
-    last wave, and plain launches instead of the CUDA graph: all bit-identical."""
+    """One sample per wave, many samples per wave (per-sample buffer + ordered sum), a ragged last wave, plain launches
+    instead of the CUDA graph, and one to four overlapped wave sequences: all bit-identical."""
     scene = _scenes.simple()
     scene.settings.samples_per_pixel = 7
     W, H = 97, 53  # not multiples of the 8x4 tile
     images = []
     for env in ({"RTR_WF_PATHS": "1024"}, {"RTR_WF_PATHS": str(97 * 53 * 3)}, {"RTR_WF_PATHS": str(1 << 21)},
                 {"RTR_WF_PATHS": str(97 * 53 * 2), "RTR_WF_GRAPH": "0"}, {"RTR_WF_REFILL_THRESHOLD": "1"},
-                {"RTR_WF_REFILL_THRESHOLD": "32"}):
+                {"RTR_WF_REFILL_THRESHOLD": "32"},
+                # one, three and four wave sequences instead of two (capi.cpp render_wavefront): the pixel sums stay in sample order
+                {"RTR_WF_LANES": "1"}, {"RTR_WF_LANES": "3", "RTR_WF_PATHS": "1024"}, {"RTR_WF_LANES": "4", "RTR_WF_PATHS": str(97 * 53)},
+                {"RTR_WF_LANES": "2", "RTR_WF_PATHS": str(97 * 53), "RTR_WF_GRAPH": "0"}):
         old = {k: os.environ.get(k) for k in env}
         os.environ.update(env)
         try:

@@ -12,7 +12,7 @@ CSRC = os.path.join(ROOT, "raytracingrust_b200", "csrc")
 
 def test_four_wide_tree_reaches_the_same_gated_leaves(tmp_path):
     exe = str(tmp_path / "check_nodes4")
-    subprocess.run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
+    subprocess.run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-pthread", "-I", os.path.join(ROOT, "include"), "-I", CSRC,
                     os.path.join(HERE, "csrc", "check_nodes4.cpp"), os.path.join(CSRC, "host_flatten.cpp"), "-o", exe], check=True)
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.startswith("OK"), r.stdout[-2000:]
