@@ -236,10 +236,13 @@ rtr_status prepare_scene(rtr_context* ctx, const rtr_scene_desc* desc, PreparedS
     // RTR_BVH_BUILD=hybrid: the device builds each mesh's reference tree (the O(n log^2 n) sorts, gates, ranks, records) and
     // the host builds the SAH traversal tree over the gates it reads back — the device's upload speed for the sorts, the
     // host tree's render speed.
-    uint32_t device_mesh_min_tris = 0;
-    bool hybrid = false;
+    // auto: meshes of 65 536 triangles or more go the hybrid way (same tree, same render speed, upload 2-2.6x faster than
+    // the threaded host build: profiles/r2/ab_hybrid_mesh_build.txt); smaller ones are built on the host in a few ms.
+    uint32_t device_mesh_min_tris = 65536;
+    bool hybrid = true;
     {
         const char* mode = std::getenv("RTR_BVH_BUILD");
+        if (mode && std::strcmp(mode, "device") == 0) hybrid = false;
         if (mode && std::strcmp(mode, "device") == 0) device_mesh_min_tris = 2;
         if (mode && std::strcmp(mode, "hybrid") == 0) { device_mesh_min_tris = 3; hybrid = true; }
         if (const char* e = std::getenv("RTR_BVH_DEVICE_MESH_MIN_TRIS")) device_mesh_min_tris = (uint32_t)std::max(0, std::atoi(e));
@@ -288,8 +291,10 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     step(upload(s, flat.sphere_info, &v.sphere_info, ctx->stream));
     step(upload(s, flat.tris, &v.tris, ctx->stream, (size_t)flat.device_tri_slots * 4));
     step(upload(s, flat.tri_vn, &v.tri_vn, ctx->stream, (size_t)flat.device_tri_slots * 3));
-    bool wide4_ok = true;
-    for (const DeviceMesh& dm : flat.device_meshes) {
+    bool hybrid = false;
+    std::vector<std::vector<F4>> mesh_sah(flat.device_meshes.size());  // hybrid: every mesh's host-built SAH tree, kept for the fold below
+    for (size_t k = 0; k < flat.device_meshes.size(); ++k) {
+        const DeviceMesh& dm = flat.device_meshes[k];
         if (e != cudaSuccess) break;
         bool nan_centroid = false, count_mismatch = false;
         std::vector<F4> gated;
@@ -298,30 +303,48 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
                                   &s->h2d_bytes, &nan_centroid, &count_mismatch, dm.hybrid ? &gated : nullptr));
         if (e == cudaSuccess && nan_centroid) { rtr_scene_destroy(s); return fail(ctx, RTR_INVALID_ARG, "rtr_scene_upload: NaN centroid (the reference panics at bvh.rs:99)"); }
         if (e == cudaSuccess && count_mismatch) { rtr_scene_destroy(s); return fail(ctx, RTR_CUDA_ERROR, "rtr_scene_upload: device mesh build emitted an unexpected number of 4-wide nodes"); }
-        if (e == cudaSuccess && dm.hybrid) {  // the host's SAH tree over the device-built gates, into the ranges reserved for it
-            std::vector<F4> sah, sah4;
-            uint32_t depth = 0, depth4 = 0;
+        if (e == cudaSuccess && dm.hybrid) {  // the host's SAH tree over the device-built gates, into the range reserved for it
+            hybrid = true;
+            uint32_t depth = 0;
             try {
-                build_traversal_over_gates(gated.data(), dm.n_tris, dm.sah_base, dm.node4_base, dm.slack, sah, sah4, &depth, &depth4);
+                build_traversal_over_gates(gated.data(), dm.n_tris, dm.sah_base, dm.slack, mesh_sah[k], &depth);
             } catch (const std::bad_alloc&) {
                 rtr_scene_destroy(s);
                 return fail(ctx, RTR_OOM, "host allocation failed while building the traversal tree");
             }
-            if (sah.size() / 4 != (size_t)dm.n_gated - 1u || sah4.size() / 8 > (size_t)dm.n_gated - 1u) {
+            if (mesh_sah[k].size() / 4 != (size_t)dm.n_gated - 1u) {
                 rtr_scene_destroy(s);
                 return fail(ctx, RTR_CUDA_ERROR, "rtr_scene_upload: the device-built gates do not match the reserved traversal-tree size");
             }
-            if (depth4 > dm.depth4_estimate) wide4_ok = false;  // deeper than the stack check assumed: this scene keeps the 2-wide walk
-            step(cudaMemcpyAsync(const_cast<F4*>(v.nodes) + (size_t)dm.sah_base * 4, sah.data(), sah.size() * sizeof(F4), cudaMemcpyHostToDevice, ctx->stream));
-            if (v.nodes4) step(cudaMemcpyAsync(const_cast<F4*>(v.nodes4) + (size_t)dm.node4_base * 8, sah4.data(), sah4.size() * sizeof(F4), cudaMemcpyHostToDevice, ctx->stream));
-            step(cudaStreamSynchronize(ctx->stream));  // sah / sah4 die here
-            s->h2d_bytes += (sah.size() + sah4.size()) * sizeof(F4);
+            step(cudaMemcpyAsync(const_cast<F4*>(v.nodes) + (size_t)dm.sah_base * 4, mesh_sah[k].data(), mesh_sah[k].size() * sizeof(F4), cudaMemcpyHostToDevice, ctx->stream));
+            s->h2d_bytes += mesh_sah[k].size() * sizeof(F4);
         }
         s->built_on_device = true;
     }
-    if (!wide4_ok) v.nodes4 = nullptr;
-    step(upload(s, flat.volumes, &v.volumes, ctx->stream));
-    step(upload(s, flat.objects, &v.objects, ctx->stream));
+    // hybrid: the 4-wide tree is folded now, over the scene level and the meshes' SAH trees together, exactly as a
+    // host-built scene's is (a mesh's top folds into the scene's nodes); volumes / objects carry the new entry refs
+    std::vector<F4> nodes4_hybrid;
+    std::vector<VolumeRec> volumes_hybrid;
+    std::vector<ObjectRec> objects_hybrid;
+    uint32_t root_entry4_hybrid = 0xFFFFFFFFu;
+    if (hybrid && e == cudaSuccess) {
+        std::vector<const std::vector<F4>*> sah_of(mesh_sah.size(), nullptr);
+        for (size_t k = 0; k < mesh_sah.size(); ++k) sah_of[k] = &mesh_sah[k];
+        uint32_t depth4 = 0;
+        try {
+            collapse_scene4(flat, sah_of, nodes4_hybrid, &root_entry4_hybrid, volumes_hybrid, objects_hybrid, &depth4);
+        } catch (const std::bad_alloc&) {
+            rtr_scene_destroy(s);
+            return fail(ctx, RTR_OOM, "host allocation failed while folding the traversal tree");
+        }
+        v.nodes4 = nullptr;
+        if (ctx->wf_wide4 != 0u && !nodes4_hybrid.empty() && 3u * depth4 + 4u <= stack_limit()) step(upload(s, nodes4_hybrid, &v.nodes4, ctx->stream));
+        step(cudaStreamSynchronize(ctx->stream));  // mesh_sah / nodes4_hybrid are read by the copies above
+    }
+    const std::vector<VolumeRec>& volumes_up = hybrid ? volumes_hybrid : flat.volumes;
+    const std::vector<ObjectRec>& objects_up = hybrid ? objects_hybrid : flat.objects;
+    step(upload(s, volumes_up, &v.volumes, ctx->stream));
+    step(upload(s, objects_up, &v.objects, ctx->stream));
     step(upload(s, flat.materials, &v.materials, ctx->stream));
     {   // SkyMap texels: raw RGB goes up as it is, the float4 layout is produced on the device
         const size_t n_tex = desc->background.kind == RTR_BG_SKYMAP ? (size_t)desc->background.width * desc->background.height : 0;
@@ -348,7 +371,7 @@ rtr_status upload_prepared(rtr_context* ctx, const rtr_scene_desc* desc, const P
     }
     v.background = flat.background;
     v.root_entry = flat.root_entry;
-    v.root_entry4 = flat.root_entry4;
+    v.root_entry4 = hybrid ? root_entry4_hybrid : flat.root_entry4;
     s->root_entry_reference = flat.root_entry_reference;
     v.n_objects = (uint32_t)flat.objects.size();
     v.n_materials = (uint32_t)flat.materials.size();

@@ -437,6 +437,11 @@ struct Flattener {
             *depth = m->hybrid ? m->depth4_estimate : levels_of(m->n_tris) / 2u + 2u;
             return RTR_MAKE_REF(REF_NODE, m->node4_base);
         }
+        // a 2-wide node folds the same way wherever it is reached from: the scene tree and the per-object entries of the
+        // linear scan share the 4-wide subtrees below the nodes they have in common
+        const size_t local2 = RTR_REF_INDEX(entry) - out.device_nodes;
+        if (memo4_ref.size() < out.nodes.size() / 4) { memo4_ref.resize(out.nodes.size() / 4, REF_EMPTY_VALUE); memo4_depth.resize(out.nodes.size() / 4, 0u); }
+        if (memo4_ref[local2] != REF_EMPTY_VALUE) { *depth = memo4_depth[local2]; return memo4_ref[local2]; }
         std::vector<Slot> s;
         slots_of(RTR_REF_INDEX(entry), s);
         for (;;) {
@@ -476,8 +481,10 @@ struct Flattener {
         }
         q[0].w = bits(refs[0]); q[1].w = bits(refs[1]); q[2].w = bits(refs[2]); q[3].w = bits(refs[3]);
         *depth = deepest + 1;
+        memo4_ref[local2] = RTR_MAKE_REF(REF_NODE, idx); memo4_depth[local2] = deepest + 1;
         return RTR_MAKE_REF(REF_NODE, idx);
     }
+    std::vector<uint32_t> memo4_ref, memo4_depth;  // by 2-wide node: its 4-wide node and depth, once folded
 
     // ---- leaves -------------------------------------------------------------
     Built emit_sphere(uint32_t sphere_index, uint32_t object) {
@@ -710,10 +717,10 @@ uint32_t count_gated(uint32_t n) {
     return (uint32_t)total;
 }
 
-void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t node_base, uint32_t node4_base, uint32_t slack,
-                                std::vector<F4>& nodes, std::vector<F4>& nodes4, uint32_t* depth, uint32_t* depth4) {
+void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t node_base, uint32_t slack, std::vector<F4>& nodes,
+                                uint32_t* depth) {
     HostFlat tmp;
-    tmp.device_nodes = node_base; tmp.device_nodes4 = node4_base;  // the Flattener numbers its nodes from these
+    tmp.device_nodes = node_base;  // the Flattener numbers its nodes from here
     rtr_scene_desc none;
     std::memset(&none, 0, sizeof(none));
     std::string err;
@@ -731,10 +738,30 @@ void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t 
     uint32_t levels = 0;
     while ((size_t(1) << levels) < n_positions) ++levels;
     const Flattener::FastOut o = f.build_traversal(L, 0, L.size(), levels + slack);  // as build_collection does for a host-built mesh
-    uint32_t d4 = 0;
-    f.collapse4(o.ref, &d4);
-    nodes.swap(tmp.nodes); nodes4.swap(tmp.nodes4);
-    *depth = o.depth; *depth4 = d4;
+    nodes.swap(tmp.nodes);
+    *depth = o.depth;
+}
+
+void collapse_scene4(const HostFlat& flat, const std::vector<const std::vector<F4>*>& mesh_sah, std::vector<F4>& nodes4,
+                     uint32_t* root_entry4, std::vector<VolumeRec>& volumes, std::vector<ObjectRec>& objects, uint32_t* max_depth4) {
+    HostFlat tmp;  // every 2-wide traversal node under its own index: nothing is external to this fold
+    tmp.nodes.assign(((size_t)flat.device_nodes) * 4 + flat.nodes.size(), F4{0, 0, 0, 0});
+    std::memcpy(tmp.nodes.data() + (size_t)flat.device_nodes * 4, flat.nodes.data(), flat.nodes.size() * sizeof(F4));
+    for (size_t k = 0; k < flat.device_meshes.size(); ++k)
+        if (flat.device_meshes[k].hybrid && mesh_sah[k])
+            std::memcpy(tmp.nodes.data() + (size_t)flat.device_meshes[k].sah_base * 4, mesh_sah[k]->data(), mesh_sah[k]->size() * sizeof(F4));
+    rtr_scene_desc none;
+    std::memset(&none, 0, sizeof(none));
+    std::string err;
+    Flattener f(tmp, none, err);
+    volumes = flat.volumes; objects = flat.objects;
+    uint32_t d4 = 0, v_depth4 = 0;
+    *root_entry4 = f.collapse4(flat.root_entry, &d4);
+    *max_depth4 = d4;
+    for (VolumeRec& v : volumes) { v.entry4 = f.collapse4(v.entry, &d4); v_depth4 = std::max(v_depth4, d4); }
+    for (ObjectRec& o : objects) { o.entry4 = f.collapse4(o.entry, &d4); *max_depth4 = std::max(*max_depth4, d4); }
+    *max_depth4 += v_depth4;
+    nodes4.swap(tmp.nodes4);
 }
 
 int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint32_t slack, uint32_t device_mesh_min_tris, bool hybrid) {
@@ -754,8 +781,8 @@ int flatten_scene(const rtr_scene_desc& d, HostFlat& out, std::string& err, uint
                 dm.hybrid = 1u;
                 dm.n_gated = count_gated(n);
                 dm.sah_base = out.device_nodes;
-                out.device_nodes += dm.n_gated - 1u;    // a binary tree over n_gated entries
-                out.device_nodes4 += dm.n_gated - 1u;   // its 4-wide collapse has at most as many nodes
+                out.device_nodes += dm.n_gated - 1u;    // a binary tree over n_gated entries; the 4-wide tree of a hybrid
+                                                        // scene is folded as a whole at upload time (collapse_scene4)
                 uint32_t levels = 0;
                 while ((1ull << levels) < n) ++levels;
                 dm.depth4_estimate = (levels + slack) / 2u + 2u;  // checked against the tree actually built at upload time

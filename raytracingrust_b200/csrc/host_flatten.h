@@ -20,15 +20,21 @@ struct DeviceMesh {
     uint32_t node4_base;   // first 4-wide node; the mesh owns count_nodes4(n_tris)
     uint32_t rank_base;    // DFS leaf rank of its first triangle (bvh.rs:183-187 tie rule)
     // hybrid: the device builds the reference tree (gates, ranks, records), the host then builds the SAH traversal tree over
-    // the gates it reads back (build_traversal_over_gates): n_gated - 1 nodes from sah_base, its 4-wide collapse from node4_base
+    // the gates it reads back (build_traversal_over_gates): n_gated - 1 nodes from sah_base
     uint32_t hybrid, sah_base, n_gated, slack, depth4_estimate;
 };
 uint32_t count_nodes4(uint32_t n_leaves);  // 4-wide nodes the device collapse emits for a median-split tree of n leaves
 uint32_t count_gated(uint32_t n_leaves);   // gated entries of that tree: single leaves + 2-leaf Splits (paired leaves)
-// SAH traversal tree + its 4-wide collapse over gated entries read back from the device (2 x F4 per leaf position:
-// {gate.min, bits(ref)} {gate.max, 0}; ref EMPTY = the second leaf of a pair).  Node indices start at node_base / node4_base.
-void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t node_base, uint32_t node4_base, uint32_t slack,
-                                std::vector<F4>& nodes, std::vector<F4>& nodes4, uint32_t* depth, uint32_t* depth4);
+// SAH traversal tree over gated entries read back from the device (2 x F4 per leaf position: {gate.min, bits(ref)}
+// {gate.max, 0}; ref EMPTY = the second leaf of a pair).  Node indices start at node_base; n_gated - 1 nodes come out.
+void build_traversal_over_gates(const F4* gated, uint32_t n_positions, uint32_t node_base, uint32_t slack, std::vector<F4>& nodes,
+                                uint32_t* depth);
+struct HostFlat;
+// Hybrid scenes: the 4-wide fold of the WHOLE traversal tree (scene level + every mesh's SAH tree, mesh_sah[k] for
+// device_meshes[k]) once those exist, so that a mesh's top folds into the scene's nodes as in a host-built scene.
+// Returns the node array (indices from 0) and the entry refs (root, VolumeRec::entry4, ObjectRec::entry4 in the copies).
+void collapse_scene4(const HostFlat& flat, const std::vector<const std::vector<F4>*>& mesh_sah, std::vector<F4>& nodes4,
+                     uint32_t* root_entry4, std::vector<VolumeRec>& volumes, std::vector<ObjectRec>& objects, uint32_t* max_depth4);
 
 struct HostFlat {
     std::vector<DeviceMesh> device_meshes;

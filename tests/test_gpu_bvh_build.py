@@ -169,6 +169,12 @@ def test_device_mesh_build_is_faster_to_upload_on_a_large_mesh(ctx):
     rays = _scenes.random_rays(1 << 16, 9, 3.0)
     assert dev.trace_batch(rays).tobytes() == host.trace_batch(rays).tobytes()
     assert hyb.trace_batch(rays).tobytes() == host.trace_batch(rays).tobytes()
+    # auto: a mesh this large takes the hybrid way (capi.cpp prepare_scene), small ones stay on the host
+    auto = ctx.upload(s)
+    assert auto.info()["n_nodes"] == hyb.info()["n_nodes"] != host.info()["n_nodes"]
+    assert auto.trace_batch(rays).tobytes() == host.trace_batch(rays).tobytes()
+    small = _scenes.mesh_bench()
+    assert ctx.upload(small).info()["n_nodes"] == upload(ctx, small, "host").info()["n_nodes"]
 
 
 def test_device_mesh_build_rejects_nan_like_the_reference_panics(ctx):
